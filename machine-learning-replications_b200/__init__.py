@@ -1,0 +1,7 @@
+"""B200-native scorer for the heart-failure-progression stack (one hot path: batched predict_proba / predict).
+
+The directory name carries a hyphen, so import it with ``importlib.import_module("machine-learning-replications_b200")``
+or through the ``mlr_b200`` alias module at the repository root.
+"""
+from .schema import N_FEATURES, load_cohort_mat, patient_vector  # noqa: F401
+from . import export, synth  # noqa: F401
