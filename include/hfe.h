@@ -1,0 +1,127 @@
+/*
+ * hfe.h -- C ABI of the B200 (sm_100a) scorer for the heart-failure-progression stack.
+ *
+ * The reference has no FFI boundary of its own: predict_hf.py:33-36 and train_ensemble_public.py:61-63 call the
+ * scikit-learn estimator protocol (predict_proba / predict / decision_function / transform / apply) on an unpickled
+ * StackingClassifier.  Each entry point below names the reference call (file:line) or scikit-learn method
+ * (SK/ = site-packages/sklearn, version 1.9.0) whose arithmetic it replaces.  The Python facade
+ * (machine-learning-replications_b200/facade.py) binds these with ctypes and presents the estimator protocol again.
+ *
+ * Conventions
+ *   - every function returns an hfe_status (0 = HFE_OK); nothing throws across the boundary;
+ *     hfe_last_error_string() gives the text for the calling thread's last failure.
+ *   - pointers named x, out, labels, ... in the *device* entry points are CUDA device pointers on the model's
+ *     device; `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream).  Device entry points
+ *     only enqueue work: they neither allocate nor synchronise.
+ *   - feature matrices are COLUMN-major float32: feature f of row i lives at x[f*ld + i], ld >= n, ld % 4 == 0 and x
+ *     16-byte aligned so that a thread can fetch four consecutive rows of one column with one 128-bit load.
+ *   - `status` is a device array of HFE_STATUS_WORDS uint32 that the call zeroes and then fills:
+ *       [0] error bits (HFE_ROW_NONFINITE if any input value was NaN/Inf -- scikit-learn raises ValueError there,
+ *           SK/svm/_base.py:652-660), [1] number of rows that were re-evaluated in float64 (see DESIGN.md,
+ *           "guard bands"), [2..3] reserved.
+ *   - a model handle is immutable after creation and may be shared by host threads and streams.
+ */
+#ifndef HFE_H_
+#define HFE_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum hfe_status {
+    HFE_OK = 0,
+    HFE_ERR_INVALID_ARGUMENT = 1,  /* null pointer, negative size, misaligned matrix */
+    HFE_ERR_BAD_BLOB = 2,          /* malformed / corrupted model blob (magic, sizes, checksum, tree shape, ...) */
+    HFE_ERR_UNSUPPORTED = 3,       /* well-formed model this build does not implement (feature count, member mix) */
+    HFE_ERR_CUDA = 4,              /* a CUDA runtime call failed; see hfe_last_error_string() */
+    HFE_ERR_NONFINITE_INPUT = 5,   /* host entry points: X holds NaN/Inf (what scikit-learn reports as ValueError) */
+    HFE_ERR_TOO_LARGE = 6          /* request exceeds a documented fixed limit */
+} hfe_status;
+
+#define HFE_N_FEATURES 17          /* load_data_public.py schema after feature selection; predict_hf.py:6-26 */
+#define HFE_STATUS_WORDS 4
+#define HFE_ROW_NONFINITE 1u
+
+typedef struct hfe_model hfe_model;
+
+typedef struct hfe_model_info {
+    int32_t n_features;
+    int32_t n_members;             /* meta-feature columns, in estimators_ order */
+    int32_t member_kind[4];        /* 1 = scaler+RBF-SVC, 2 = boosted trees, 3 = logistic regression, 0 = unused */
+    int32_t n_support_vectors;
+    int32_t n_trees;
+    int32_t n_tree_nodes;
+    int32_t max_tree_depth;
+    int32_t tree_mode;             /* 0 none, 1 depth-1 stumps merged into a split table, 2 general node tables */
+    int32_t n_merged_splits;
+    int32_t device;
+    int32_t reserved;
+    double  svc_guard;             /* |decision value| uncertainty assumed for the float32 RBF sum */
+    uint64_t device_bytes;         /* bytes of device memory the handle owns */
+} hfe_model_info;
+
+/* Replaces pickle.load('./hf_predict_model.pkl') (predict_hf.py:33-34): validates the flat blob written by
+ * export/blob.py (header, CRC-32, section shapes, tree topology, the n_support consistency check of
+ * SK/svm/_base.py:680-686), derives the device tables and uploads them to `device`.  Allocates; call once. */
+int hfe_model_create(const void* blob, size_t blob_bytes, int device, hfe_model** out_model);
+void hfe_model_destroy(hfe_model* model);
+int hfe_model_get_info(const hfe_model* model, hfe_model_info* out_info);
+
+/* StackingClassifier.predict_proba (SK/ensemble/_stacking.py:768-794) as called at predict_hf.py:36 and
+ * train_ensemble_public.py:62.  out_n2[2*i] = P(class 0) = 1 - p1, out_n2[2*i+1] = p1, float32.
+ * One fused kernel: scaler -> RBF-SVC decision -> Platt -> clamp -> 2-class coupling (svm.cpp:2921-2958, 2046-2107),
+ * boosted trees (_gradient_boosting.pyx:25-73) -> expit, logistic member (_base.py:366-451), combiner. */
+int hfe_predict_proba(const hfe_model* model, const float* x, int64_t n, int64_t ld, float* out_n2,
+                      uint32_t* status, void* stream);
+
+/* StackingClassifier.predict (SK/ensemble/_stacking.py:711-766 -> SK/linear_model/_base.py:398-425): labels[i] = 1
+ * iff the combiner's decision value is strictly > 0 (index into classes_).  out_n2 may be NULL. */
+int hfe_predict(const hfe_model* model, const float* x, int64_t n, int64_t ld, uint8_t* labels, float* out_n2,
+                uint32_t* status, void* stream);
+
+/* Everything at once; any output pointer may be NULL.  decision[i] is the combiner's float64 decision value
+ * (StackingClassifier.decision_function), meta[i*n_members + m] the float64 P(class 1) of member m
+ * (StackingClassifier.transform, SK/ensemble/_stacking.py:814-830, 87-135).
+ * perm_col >= 0 scores the matrix with column perm_col read through perm_idx (int32 row indices, length n): one pass
+ * of permutation importance (SK/inspection/_permutation_importance.py:31-76) without materialising the shuffled
+ * matrix.  If y (uint8 class indices) and score are given, score[0] += #{labels == y} (uint64) is accumulated. */
+int hfe_score(const hfe_model* model, const float* x, int64_t n, int64_t ld, int32_t perm_col,
+              const int32_t* perm_idx, float* out_n2, uint8_t* labels, double* decision, double* meta,
+              const uint8_t* y, unsigned long long* score, uint32_t* status, void* stream);
+
+/* GradientBoostingClassifier.apply (SK/ensemble/_gb.py:1104-1135; SK/tree/_tree.pyx:954-996): scikit-learn node id of
+ * the leaf each row reaches in each tree, leaves[i*n_trees + t], uint16 (parity mode; not on the timed path). */
+int hfe_apply(const hfe_model* model, const float* x, int64_t n, int64_t ld, uint16_t* leaves, void* stream);
+
+/* Same as evaluating every row through the float64 re-evaluation path (test / calibration aid). */
+int hfe_predict_proba_f64(const hfe_model* model, const float* x, int64_t n, int64_t ld, double* out_n2,
+                          uint32_t* status, void* stream);
+
+/* Synthetic cohort rows on the device (the reference's .mat cohorts are unpublished): column c of row (row0+i) is
+ * base[c] + step[c] * #{k : hash32(seed,row,col_id[c]) >= thr[k]}, k in [thr_off[c], thr_off[c+1]).  All table
+ * pointers are DEVICE pointers.  Bit-identical to synth.host_rows(). */
+int hfe_synth_rows(uint64_t seed, int64_t row0, int64_t n, int32_t n_cols, const int32_t* col_id, const float* base,
+                   const float* step, const int32_t* thr_off, const uint32_t* thr, float* x, int64_t ld,
+                   void* stream);
+
+/* Row-major float64 [n, n_features] (what load_data_public.py:11-14 yields and predict_hf.py:36 passes) ->
+ * column-major float32 with round-to-nearest, the cast SK/ensemble/_gb.py:1579-1604 applies; sets HFE_ROW_NONFINITE. */
+int hfe_ingest_rowmajor_f64(const double* x_rowmajor, int64_t n, int32_t n_features, float* x, int64_t ld,
+                            uint32_t* status, void* stream);
+
+/* Host-buffer convenience used by the facade for numpy inputs: copies X (row-major float64, host) to the device,
+ * ingests, scores, copies P back (float64 [n,2]; p0 = 1 - p1) and synchronises.  Allocates temporaries.
+ * labels / decision / meta may be NULL.  Returns HFE_ERR_NONFINITE_INPUT when X holds NaN/Inf. */
+int hfe_predict_host(const hfe_model* model, const double* x_rowmajor, int64_t n, double* proba_n2, uint8_t* labels,
+                     double* decision, double* meta);
+
+const char* hfe_last_error_string(void);
+int hfe_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HFE_H_ */

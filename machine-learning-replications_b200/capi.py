@@ -1,0 +1,77 @@
+"""ctypes binding of ``libhfe.so`` (include/hfe.h).  There is no CPU fallback: if the library is missing, or a call
+fails, an exception is raised."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libhfe.so")
+
+HFE_OK = 0
+HFE_ERR_NONFINITE_INPUT = 5
+STATUS_WORDS = 4
+ROW_NONFINITE = 1
+
+EXPORTS = [
+    "hfe_abi_version", "hfe_last_error_string", "hfe_model_create", "hfe_model_destroy", "hfe_model_get_info",
+    "hfe_predict_proba", "hfe_predict", "hfe_score", "hfe_apply", "hfe_predict_proba_f64", "hfe_synth_rows",
+    "hfe_ingest_rowmajor_f64", "hfe_predict_host",
+]
+
+
+class HfeError(RuntimeError):
+    def __init__(self, code, message):
+        super().__init__(f"hfe status {code}: {message}")
+        self.code = code
+
+
+class ModelInfo(C.Structure):
+    _fields_ = [
+        ("n_features", C.c_int32), ("n_members", C.c_int32), ("member_kind", C.c_int32 * 4),
+        ("n_support_vectors", C.c_int32), ("n_trees", C.c_int32), ("n_tree_nodes", C.c_int32),
+        ("max_tree_depth", C.c_int32), ("tree_mode", C.c_int32), ("n_merged_splits", C.c_int32),
+        ("device", C.c_int32), ("reserved", C.c_int32), ("svc_guard", C.c_double), ("device_bytes", C.c_uint64),
+    ]
+
+
+_lib = None
+
+
+def load_library(path: str = LIB_PATH):
+    """Load (once) and type the C ABI.  Raises ``FileNotFoundError`` with build instructions when it is absent."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(path):
+        raise FileNotFoundError(
+            f"{path} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc -gencode arch=compute_100a,code=sm_100a); this package has no CPU fallback")
+    lib = C.CDLL(path)
+    vp, i64, i32, u64 = C.c_void_p, C.c_int64, C.c_int32, C.c_uint64
+    lib.hfe_abi_version.restype = C.c_int
+    lib.hfe_last_error_string.restype = C.c_char_p
+    lib.hfe_model_create.argtypes = [vp, C.c_size_t, C.c_int, C.POINTER(vp)]
+    lib.hfe_model_destroy.argtypes = [vp]
+    lib.hfe_model_destroy.restype = None
+    lib.hfe_model_get_info.argtypes = [vp, C.POINTER(ModelInfo)]
+    lib.hfe_predict_proba.argtypes = [vp, vp, i64, i64, vp, vp, vp]
+    lib.hfe_predict.argtypes = [vp, vp, i64, i64, vp, vp, vp, vp]
+    lib.hfe_score.argtypes = [vp, vp, i64, i64, i32, vp, vp, vp, vp, vp, vp, vp, vp, vp]
+    lib.hfe_apply.argtypes = [vp, vp, i64, i64, vp, vp]
+    lib.hfe_predict_proba_f64.argtypes = [vp, vp, i64, i64, vp, vp, vp]
+    lib.hfe_synth_rows.argtypes = [u64, i64, i64, i32, vp, vp, vp, vp, vp, vp, i64, vp]
+    lib.hfe_ingest_rowmajor_f64.argtypes = [vp, i64, i32, vp, i64, vp, vp]
+    lib.hfe_predict_host.argtypes = [vp, vp, i64, vp, vp, vp, vp]
+    for name in EXPORTS:
+        fn = getattr(lib, name)
+        if name not in ("hfe_last_error_string", "hfe_model_destroy"):
+            fn.restype = C.c_int
+    _lib = lib
+    return lib
+
+
+def check(code: int):
+    if code != HFE_OK:
+        msg = load_library().hfe_last_error_string()
+        raise HfeError(code, msg.decode("utf-8", "replace") if msg else "")

@@ -1,0 +1,286 @@
+// hfe_api.cu -- the extern "C" boundary declared in include/hfe.h.  Plain pointers and sizes in, status codes out.
+#include <cstdio>
+#include <cstdlib>
+#include <mutex>
+#include <new>
+
+#include "hfe_kernels.cuh"
+
+using namespace hfe;
+
+struct hfe_model {
+    Model* impl;
+};
+
+namespace {
+
+int check_matrix(const hfe_model* model, const float* x, int64_t n, int64_t ld) {
+    if (!model || !model->impl) return fail(HFE_ERR_INVALID_ARGUMENT, "null model handle");
+    if (n < 0) return fail(HFE_ERR_INVALID_ARGUMENT, "negative row count");
+    if (n > 0 && !x) return fail(HFE_ERR_INVALID_ARGUMENT, "null feature matrix");
+    if (ld < n) return fail(HFE_ERR_INVALID_ARGUMENT, "leading dimension smaller than the row count");
+    if ((ld & 3) || (reinterpret_cast<uintptr_t>(x) & 15))
+        return fail(HFE_ERR_INVALID_ARGUMENT, "feature matrix must be 16-byte aligned with ld % 4 == 0");
+    if (n > (int64_t)2147483647 * 256) return fail(HFE_ERR_TOO_LARGE, "more rows than one launch can address");
+    return HFE_OK;
+}
+
+template <bool SVC, int TM>
+int launch_score(const Model* m, const ScoreParams& P, cudaStream_t stream) {
+    size_t sv_bytes = 0;
+    int smem_groups = 0;
+    if (SVC) {
+        smem_groups = std::min(P.n_groups, TM == 2 ? 256 : MAX_SMEM_GROUPS);
+        sv_bytes = (size_t)smem_groups * SV_ROWS * sizeof(float4);
+    }
+    size_t smem = sv_bytes + (TM == 2 ? (size_t)F * BLOCK_ROWS * sizeof(float) : 0);
+    auto kernel = hfe_score_kernel<SVC, TM>;
+    static std::once_flag once[16];        // per device: opt in to large dynamic shared memory once
+    static cudaError_t attr_err[16];
+    int dev = m->device & 15;
+    std::call_once(once[dev], [&] {
+        attr_err[dev] = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    });
+    if (attr_err[dev] != cudaSuccess)
+        return fail(HFE_ERR_CUDA, std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(attr_err[dev]));
+    long long blocks = (P.n + BLOCK_ROWS - 1) / BLOCK_ROWS;
+    kernel<<<(unsigned)blocks, BLOCK_THREADS, smem, stream>>>(P, smem_groups);
+    HFE_CUDA_TRY(cudaGetLastError());
+    return HFE_OK;
+}
+
+int dispatch_score(const Model* m, const ScoreParams& P, cudaStream_t stream) {
+    bool svc = P.slot_svc >= 0;
+    switch (m->tree_mode * 2 + (svc ? 1 : 0)) {
+        case 0: return launch_score<false, 0>(m, P, stream);
+        case 1: return launch_score<true, 0>(m, P, stream);
+        case 2: return launch_score<false, 1>(m, P, stream);
+        case 3: return launch_score<true, 1>(m, P, stream);
+        case 4: return launch_score<false, 2>(m, P, stream);
+        default: return launch_score<true, 2>(m, P, stream);
+    }
+}
+
+int score_common(const hfe_model* model, const float* x, int64_t n, int64_t ld, int32_t perm_col,
+                 const int32_t* perm_idx, float* out, double* out64, uint8_t* labels, double* decision, double* meta,
+                 const uint8_t* y, unsigned long long* score, uint32_t* status, void* stream, bool all_f64) {
+    int rc = check_matrix(model, x, n, ld);
+    if (rc) return rc;
+    if (!status) return fail(HFE_ERR_INVALID_ARGUMENT, "null status array");
+    if (perm_col >= F || (perm_col >= 0 && !perm_idx))
+        return fail(HFE_ERR_INVALID_ARGUMENT, "bad permutation column / index array");
+    if ((y != nullptr) != (score != nullptr)) return fail(HFE_ERR_INVALID_ARGUMENT, "y and score go together");
+    const Model* m = model->impl;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    HFE_CUDA_TRY(cudaSetDevice(m->device));
+    HFE_CUDA_TRY(cudaMemsetAsync(status, 0, HFE_STATUS_WORDS * sizeof(uint32_t), s));
+    if (n == 0) return HFE_OK;
+    ScoreParams P = m->base;
+    P.x = x;
+    P.n = n;
+    P.ld = ld;
+    P.perm_col = perm_col < 0 ? -1 : perm_col;
+    P.perm_idx = perm_idx;
+    P.out = out;
+    P.out64 = out64;
+    P.labels = labels;
+    P.decision = decision;
+    P.meta = meta;
+    P.y = y;
+    P.score = score;
+    P.status = status;
+    if (all_f64) {
+        long long blocks = std::min<long long>(n, 148LL * 64);
+        hfe_score_f64_kernel<<<(unsigned)blocks, BLOCK_THREADS, 0, s>>>(P);
+        HFE_CUDA_TRY(cudaGetLastError());
+        return HFE_OK;
+    }
+    return dispatch_score(m, P, s);
+}
+
+}  // namespace
+
+extern "C" {
+
+int hfe_abi_version(void) { return 1; }
+
+const char* hfe_last_error_string(void) { return g_last_error.c_str(); }
+
+int hfe_model_create(const void* blob, size_t blob_bytes, int device, hfe_model** out_model) {
+    if (!blob || !out_model) return fail(HFE_ERR_INVALID_ARGUMENT, "null blob or output pointer");
+    *out_model = nullptr;
+    if (device < 0) return fail(HFE_ERR_INVALID_ARGUMENT, "negative device ordinal");
+    // aligned private copy: sections are read through double* / int32_t*
+    std::vector<uint64_t> copy((blob_bytes + 7) / 8 + 1, 0);
+    std::memcpy(copy.data(), blob, blob_bytes);
+    Model* impl = nullptr;
+    int rc = build_model(reinterpret_cast<const uint8_t*>(copy.data()), blob_bytes, device, &impl);
+    if (rc) return rc;
+    hfe_model* h = new (std::nothrow) hfe_model{impl};
+    if (!h) return fail(HFE_ERR_INVALID_ARGUMENT, "out of host memory");
+    *out_model = h;
+    return HFE_OK;
+}
+
+void hfe_model_destroy(hfe_model* model) {
+    if (!model) return;
+    if (model->impl) {
+        cudaSetDevice(model->impl->device);
+        for (void* p : model->impl->allocations) cudaFree(p);
+        delete model->impl;
+    }
+    delete model;
+}
+
+int hfe_model_get_info(const hfe_model* model, hfe_model_info* info) {
+    if (!model || !model->impl || !info) return fail(HFE_ERR_INVALID_ARGUMENT, "null model or info pointer");
+    const Model* m = model->impl;
+    std::memset(info, 0, sizeof(*info));
+    info->n_features = F;
+    info->n_members = m->n_members;
+    for (int i = 0; i < 4; ++i) info->member_kind[i] = m->kinds[i];
+    info->n_support_vectors = m->n_sv;
+    info->n_trees = m->n_trees;
+    info->n_tree_nodes = m->n_nodes;
+    info->max_tree_depth = m->max_depth;
+    info->tree_mode = m->tree_mode;
+    info->n_merged_splits = m->n_splits;
+    info->device = m->device;
+    info->svc_guard = m->svc_guard;
+    info->device_bytes = m->device_bytes;
+    return HFE_OK;
+}
+
+int hfe_predict_proba(const hfe_model* model, const float* x, int64_t n, int64_t ld, float* out_n2, uint32_t* status,
+                      void* stream) {
+    if (n > 0 && !out_n2) return fail(HFE_ERR_INVALID_ARGUMENT, "null output");
+    return score_common(model, x, n, ld, -1, nullptr, out_n2, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr,
+                        status, stream, false);
+}
+
+int hfe_predict(const hfe_model* model, const float* x, int64_t n, int64_t ld, uint8_t* labels, float* out_n2,
+                uint32_t* status, void* stream) {
+    if (n > 0 && !labels) return fail(HFE_ERR_INVALID_ARGUMENT, "null labels");
+    return score_common(model, x, n, ld, -1, nullptr, out_n2, nullptr, labels, nullptr, nullptr, nullptr, nullptr,
+                        status, stream, false);
+}
+
+int hfe_score(const hfe_model* model, const float* x, int64_t n, int64_t ld, int32_t perm_col,
+              const int32_t* perm_idx, float* out_n2, uint8_t* labels, double* decision, double* meta,
+              const uint8_t* y, unsigned long long* score, uint32_t* status, void* stream) {
+    return score_common(model, x, n, ld, perm_col, perm_idx, out_n2, nullptr, labels, decision, meta, y, score, status,
+                        stream, false);
+}
+
+int hfe_predict_proba_f64(const hfe_model* model, const float* x, int64_t n, int64_t ld, double* out_n2,
+                          uint32_t* status, void* stream) {
+    if (n > 0 && !out_n2) return fail(HFE_ERR_INVALID_ARGUMENT, "null output");
+    return score_common(model, x, n, ld, -1, nullptr, nullptr, out_n2, nullptr, nullptr, nullptr, nullptr, nullptr,
+                        status, stream, true);
+}
+
+int hfe_apply(const hfe_model* model, const float* x, int64_t n, int64_t ld, uint16_t* leaves, void* stream) {
+    int rc = check_matrix(model, x, n, ld);
+    if (rc) return rc;
+    const Model* m = model->impl;
+    if (m->n_trees == 0) return fail(HFE_ERR_UNSUPPORTED, "model has no boosted-tree member");
+    if (n == 0) return HFE_OK;
+    if (!leaves) return fail(HFE_ERR_INVALID_ARGUMENT, "null output");
+    HFE_CUDA_TRY(cudaSetDevice(m->device));
+    ScoreParams P = m->base;
+    P.x = x;
+    P.n = n;
+    P.ld = ld;
+    long long blocks = (n + BLOCK_THREADS - 1) / BLOCK_THREADS;
+    hfe_apply_kernel<<<(unsigned)blocks, BLOCK_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(P, leaves);
+    HFE_CUDA_TRY(cudaGetLastError());
+    return HFE_OK;
+}
+
+int hfe_synth_rows(uint64_t seed, int64_t row0, int64_t n, int32_t n_cols, const int32_t* col_id, const float* base,
+                   const float* step, const int32_t* thr_off, const uint32_t* thr, float* x, int64_t ld,
+                   void* stream) {
+    if (n < 0 || row0 < 0 || n_cols < 1 || ld < n) return fail(HFE_ERR_INVALID_ARGUMENT, "bad synth_rows sizes");
+    if (n == 0) return HFE_OK;
+    if (!col_id || !base || !step || !thr_off || !thr || !x)
+        return fail(HFE_ERR_INVALID_ARGUMENT, "null synth_rows table");
+    long long blocks = std::min<long long>((n + BLOCK_THREADS - 1) / BLOCK_THREADS, 148LL * 16);
+    hfe_synth_kernel<<<(unsigned)blocks, BLOCK_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
+        seed, row0, n, n_cols, col_id, base, step, thr_off, thr, x, ld);
+    HFE_CUDA_TRY(cudaGetLastError());
+    return HFE_OK;
+}
+
+int hfe_ingest_rowmajor_f64(const double* x_rowmajor, int64_t n, int32_t n_features, float* x, int64_t ld,
+                            uint32_t* status, void* stream) {
+    if (n < 0 || n_features < 1 || n_features > 64 || ld < n)
+        return fail(HFE_ERR_INVALID_ARGUMENT, "bad ingest sizes");
+    if (!status) return fail(HFE_ERR_INVALID_ARGUMENT, "null status array");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    HFE_CUDA_TRY(cudaMemsetAsync(status, 0, HFE_STATUS_WORDS * sizeof(uint32_t), s));
+    if (n == 0) return HFE_OK;
+    if (!x_rowmajor || !x) return fail(HFE_ERR_INVALID_ARGUMENT, "null ingest buffer");
+    long long blocks = (n + BLOCK_THREADS - 1) / BLOCK_THREADS;
+    size_t smem = (size_t)BLOCK_THREADS * (n_features + 1) * sizeof(float);
+    hfe_ingest_kernel<<<(unsigned)blocks, BLOCK_THREADS, smem, s>>>(x_rowmajor, n, n_features, x, ld, status);
+    HFE_CUDA_TRY(cudaGetLastError());
+    return HFE_OK;
+}
+
+int hfe_predict_host(const hfe_model* model, const double* x_rowmajor, int64_t n, double* proba_n2, uint8_t* labels,
+                     double* decision, double* meta) {
+    if (!model || !model->impl) return fail(HFE_ERR_INVALID_ARGUMENT, "null model handle");
+    if (n < 0) return fail(HFE_ERR_INVALID_ARGUMENT, "negative row count");
+    if (n == 0) return HFE_OK;
+    if (!x_rowmajor) return fail(HFE_ERR_INVALID_ARGUMENT, "null input");
+    const Model* m = model->impl;
+    HFE_CUDA_TRY(cudaSetDevice(m->device));
+    int64_t ld = (n + 3) & ~(int64_t)3;
+    size_t in_bytes = (size_t)n * F * sizeof(double);
+    size_t col_bytes = (size_t)ld * F * sizeof(float);
+    size_t out_bytes = (size_t)n * 2 * sizeof(float);
+    size_t dec_bytes = decision ? (size_t)n * sizeof(double) : 0;
+    size_t meta_bytes = meta ? (size_t)n * m->n_members * sizeof(double) : 0;
+    size_t lab_bytes = labels ? (size_t)n : 0;
+    auto up = [](size_t b) { return (b + 255) & ~(size_t)255; };
+    size_t total = up(in_bytes) + up(col_bytes) + up(out_bytes) + up(dec_bytes) + up(meta_bytes) + up(lab_bytes) + 256;
+    unsigned char* buf = nullptr;
+    HFE_CUDA_TRY(cudaMalloc(&buf, total));
+    struct Guard { unsigned char* p; ~Guard() { cudaFree(p); } } guard{buf};
+    unsigned char* cur = buf;
+    auto take = [&](size_t b) { unsigned char* p = cur; cur += up(b); return p; };
+    double* d_in = reinterpret_cast<double*>(take(in_bytes));
+    float* d_x = reinterpret_cast<float*>(take(col_bytes));
+    float* d_out = reinterpret_cast<float*>(take(out_bytes));
+    double* d_dec = decision ? reinterpret_cast<double*>(take(dec_bytes)) : nullptr;
+    double* d_meta = meta ? reinterpret_cast<double*>(take(meta_bytes)) : nullptr;
+    uint8_t* d_lab = labels ? take(lab_bytes) : nullptr;
+    uint32_t* d_status = reinterpret_cast<uint32_t*>(take(2 * HFE_STATUS_WORDS * sizeof(uint32_t)));
+    cudaStream_t s = nullptr;
+    HFE_CUDA_TRY(cudaMemcpyAsync(d_in, x_rowmajor, in_bytes, cudaMemcpyHostToDevice, s));
+    int rc = hfe_ingest_rowmajor_f64(d_in, n, F, d_x, ld, d_status, s);
+    if (rc) return rc;
+    rc = score_common(model, d_x, n, ld, -1, nullptr, d_out, nullptr, d_lab, d_dec, d_meta, nullptr, nullptr,
+                      d_status + HFE_STATUS_WORDS, s, false);
+    if (rc) return rc;
+    std::vector<float> host_out((size_t)n * 2);
+    uint32_t host_status[2 * HFE_STATUS_WORDS];
+    HFE_CUDA_TRY(cudaMemcpyAsync(host_out.data(), d_out, out_bytes, cudaMemcpyDeviceToHost, s));
+    if (decision) HFE_CUDA_TRY(cudaMemcpyAsync(decision, d_dec, dec_bytes, cudaMemcpyDeviceToHost, s));
+    if (meta) HFE_CUDA_TRY(cudaMemcpyAsync(meta, d_meta, meta_bytes, cudaMemcpyDeviceToHost, s));
+    if (labels) HFE_CUDA_TRY(cudaMemcpyAsync(labels, d_lab, lab_bytes, cudaMemcpyDeviceToHost, s));
+    HFE_CUDA_TRY(cudaMemcpyAsync(host_status, d_status, sizeof(host_status), cudaMemcpyDeviceToHost, s));
+    HFE_CUDA_TRY(cudaStreamSynchronize(s));
+    if ((host_status[0] | host_status[HFE_STATUS_WORDS]) & HFE_ROW_NONFINITE)
+        return fail(HFE_ERR_NONFINITE_INPUT, "Input X contains NaN or infinity");
+    if (proba_n2) {
+        for (int64_t i = 0; i < n; ++i) {
+            double p1 = (double)host_out[2 * i + 1];
+            proba_n2[2 * i] = 1.0 - p1;
+            proba_n2[2 * i + 1] = p1;
+        }
+    }
+    return HFE_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,552 @@
+// hfe_model.cuh -- host side of the model handle: blob validation and the derived device tables.
+//
+// The blob (export/blob.py) carries scikit-learn's canonical float64 parameters.  Everything the kernels read is
+// derived here, once, so that every rounding decision lives in one place:
+//   * RBF-SVC (SK/svm/src/libsvm/svm.cpp:461-515, 2821-2904): exp(-g|z-s|^2) = 2^(2c z.s) * 2^(-c|s|^2) * 2^(-c|z|^2),
+//     c = g*log2(e).  Per support vector the float32 table holds w = 2c*s (17 values) and coef' = coef * 2^(-c|s|^2);
+//     the row factor 2^(-c|z|^2) is applied once in float64.  Support vectors are re-ordered so positive and negative
+//     coefficients alternate (running sum near zero): the float32 partial sums stay small, which is what bounds the
+//     accumulation error (DESIGN.md "error budget").
+//   * boosted trees (SK/ensemble/_gradient_boosting.pyx:25-73): thresholds rounded toward -inf to float32 so that
+//     (x32 <= thr32) == ((double)x32 <= thr64) for every float32 x -- leaf indices stay bit-exact; nodes re-laid in
+//     breadth-first order with siblings adjacent (next = child + (x > thr)), leaves made self-looping so a fixed-depth
+//     predicated walk needs no per-lane exit test; leaf values pre-multiplied by the learning rate in float64.
+//   * depth-1 stumps with few distinct (feature, threshold) pairs are merged into a split table (100 published
+//     stumps -> 17 splits).
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/hfe.h"
+#include "hfe_solver.cuh"
+
+namespace hfe {
+
+constexpr int F = HFE_N_FEATURES;
+constexpr int MAX_MEMBERS = 4;
+constexpr int MAX_SPLITS = 128;       // merged stump table capacity (kernel parameter space)
+constexpr int SV_GROUP = 4;           // support vectors per float4 lane group
+constexpr int SV_ROWS = F + 1;        // float4 rows per group: F weights + folded coefficient
+constexpr int MAX_EDGES = 16;          // coupling-solver discontinuities (6 exist for eps = 0.0025)
+constexpr int SV_CHUNK = 8;           // float32 partial sums are folded into float64 every SV_CHUNK vectors
+
+enum MemberKind { KIND_NONE = 0, KIND_SVC = 1, KIND_GBT = 2, KIND_LIN = 3 };
+
+// Parameter block handed to every scoring kernel by value (lives in the constant bank; fully unrolled feature loops
+// turn the small tables into immediate constant operands).
+struct ScoreParams {
+    // request
+    const float* x;
+    long long n, ld;
+    const int* perm_idx;
+    int perm_col;
+    int n_members;
+    float* out;                 // [n,2] f32 or null
+    double* out64;              // [n,2] f64 or null
+    unsigned char* labels;      // [n] or null
+    double* decision;           // [n] or null
+    double* meta;               // [n, n_members] or null
+    const unsigned char* y;     // [n] or null
+    unsigned long long* score;  // [1] or null
+    unsigned int* status;       // [HFE_STATUS_WORDS]
+    // SVC member
+    const float4* sv_tab;       // [n_groups][SV_ROWS] float4
+    const double* sv64;         // [n_sv][F] original order
+    const double* dual64;       // [n_sv]
+    int n_groups;               // multiple of SV_CHUNK / SV_GROUP
+    int n_sv;
+    double mean[F], inv_scale[F], scale[F];
+    double c_log2;              // gamma * log2(e)
+    double gamma, svc_intercept, prob_a, prob_b;
+    double zz_limit;            // rows with c|z|^2 above this go to the float64 path (float32 2^x range)
+    double solver_guard;        // Platt argument within this of a solver edge => the solver's branch is uncertain
+    double edges[MAX_EDGES];    // values of t = f*A+B where the coupling solver's sweep count changes
+    int n_edges;
+    int pad_edges_;
+    double label_guard;         // |z_final| below this => hard label is uncertain
+    // boosted trees
+    int n_trees;
+    int n_splits;
+    double gbt_init;            // init raw prediction
+    double gbt_split_base;      // init + sum of right-leaf values (merged stump mode)
+    int split_begin[F + 1];
+    float split_thr[MAX_SPLITS];
+    float split_delta[MAX_SPLITS];
+    const uint2* nodes;         // {thr32 bits, feature<<24 | child}, tree-local child index
+    const float* value32;       // lr * value, per node
+    const double* value64;
+    const int* tree_off;        // [n_trees+1]
+    const unsigned char* tree_depth;  // [n_trees]
+    const unsigned short* sk_id;      // scikit-learn node id per re-laid node
+    // logistic member
+    double lin_coef[F];
+    double lin_intercept;
+    // combiner
+    double final_coef[MAX_MEMBERS];
+    double final_intercept;
+    int slot_svc, slot_gbt, slot_lin;
+    int pad_;
+};
+
+struct Model {
+    int device = 0;
+    int n_members = 0;
+    int kinds[MAX_MEMBERS] = {0, 0, 0, 0};
+    int n_sv = 0, n_trees = 0, n_nodes = 0, max_depth = 0, tree_mode = 0, n_splits = 0;
+    double svc_guard = 0.0;       // assumed |error| of the float32 SVC decision value
+    double gbt_guard = 0.0;       // assumed |error| of the float32 boosted raw score
+    ScoreParams base{};           // request fields zero; table pointers filled
+    std::vector<void*> allocations;
+    uint64_t device_bytes = 0;
+};
+
+inline thread_local std::string g_last_error;
+
+inline int fail(int code, const std::string& msg) {
+    g_last_error = msg;
+    return code;
+}
+
+#define HFE_CUDA_TRY(expr)                                                                              \
+    do {                                                                                                \
+        cudaError_t err__ = (expr);                                                                     \
+        if (err__ != cudaSuccess)                                                                       \
+            return ::hfe::fail(HFE_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(err__));    \
+    } while (0)
+
+// ---- blob parsing ----------------------------------------------------------------------------------------------------
+
+inline uint32_t crc32_zlib(const uint8_t* p, size_t n) {
+    static uint32_t table[8][256];
+    static bool ready = false;
+    if (!ready) {
+        for (uint32_t i = 0; i < 256; ++i) {
+            uint32_t c = i;
+            for (int k = 0; k < 8; ++k) c = (c & 1) ? (0xEDB88320u ^ (c >> 1)) : (c >> 1);
+            table[0][i] = c;
+        }
+        for (uint32_t i = 0; i < 256; ++i)
+            for (int t = 1; t < 8; ++t) table[t][i] = (table[t - 1][i] >> 8) ^ table[0][table[t - 1][i] & 0xFF];
+        ready = true;
+    }
+    uint32_t c = 0xFFFFFFFFu;
+    while (n >= 8) {
+        uint32_t a, b;
+        std::memcpy(&a, p, 4);
+        std::memcpy(&b, p + 4, 4);
+        a ^= c;
+        c = table[7][a & 0xFF] ^ table[6][(a >> 8) & 0xFF] ^ table[5][(a >> 16) & 0xFF] ^ table[4][a >> 24] ^
+            table[3][b & 0xFF] ^ table[2][(b >> 8) & 0xFF] ^ table[1][(b >> 16) & 0xFF] ^ table[0][b >> 24];
+        p += 8;
+        n -= 8;
+    }
+    while (n--) c = table[0][(c ^ *p++) & 0xFF] ^ (c >> 8);
+    return c ^ 0xFFFFFFFFu;
+}
+
+struct Section {
+    const uint8_t* data = nullptr;
+    uint64_t count = 0;
+    const double* f64() const { return reinterpret_cast<const double*>(data); }
+    const int32_t* i32() const { return reinterpret_cast<const int32_t*>(data); }
+    const uint32_t* u32() const { return reinterpret_cast<const uint32_t*>(data); }
+};
+
+struct ParsedBlob {
+    uint32_t n_features = 0, n_members = 0;
+    std::map<std::pair<uint32_t, uint32_t>, Section> sections;
+    const Section* find(uint32_t kind, uint32_t member, uint64_t count) const {
+        auto it = sections.find({kind, member});
+        if (it == sections.end() || it->second.count != count) return nullptr;
+        return &it->second;
+    }
+    bool has(uint32_t kind, uint32_t member) const { return sections.count({kind, member}) != 0; }
+};
+
+enum : uint32_t {
+    K_FINAL = 1, K_CLASSES = 2, K_SVC_PARAMS = 10, K_SVC_MEAN = 11, K_SVC_SCALE = 12, K_SVC_SV = 13, K_SVC_DUAL = 14,
+    K_GBT_PARAMS = 20, K_GBT_OFFSETS = 21, K_GBT_FEATURE = 22, K_GBT_LEFT = 23, K_GBT_RIGHT = 24,
+    K_GBT_THRESHOLD = 25, K_GBT_VALUE = 26, K_LIN_PARAMS = 30, STACK_LEVEL = 0xFFFFFFFFu
+};
+
+inline int elem_size(uint32_t kind) {
+    switch (kind) {
+        case K_GBT_OFFSETS: case K_GBT_FEATURE: case K_GBT_LEFT: case K_GBT_RIGHT: return 4;
+        case K_FINAL: case K_CLASSES: case K_SVC_PARAMS: case K_SVC_MEAN: case K_SVC_SCALE: case K_SVC_SV:
+        case K_SVC_DUAL: case K_GBT_PARAMS: case K_GBT_THRESHOLD: case K_GBT_VALUE: case K_LIN_PARAMS: return 8;
+        default: return 0;
+    }
+}
+
+inline int parse_blob(const uint8_t* b, size_t len, ParsedBlob* out) {
+    if (len < 64 || std::memcmp(b, "HFEBLOB1", 8) != 0) return fail(HFE_ERR_BAD_BLOB, "blob: bad magic or truncated");
+    uint32_t version, hbytes, crc, nf, nm, ns;
+    uint64_t total;
+    std::memcpy(&version, b + 8, 4);
+    std::memcpy(&hbytes, b + 12, 4);
+    std::memcpy(&total, b + 16, 8);
+    std::memcpy(&crc, b + 24, 4);
+    std::memcpy(&nf, b + 28, 4);
+    std::memcpy(&nm, b + 32, 4);
+    std::memcpy(&ns, b + 36, 4);
+    if (version != 1 || hbytes != 64) return fail(HFE_ERR_BAD_BLOB, "blob: unknown version");
+    if (total != len) return fail(HFE_ERR_BAD_BLOB, "blob: total_bytes does not match the buffer length");
+    if (nf < 1 || nf > 4096 || nm < 1 || nm > 16 || ns < 2 || ns > 256)
+        return fail(HFE_ERR_BAD_BLOB, "blob: implausible header counts");
+    uint64_t pay0 = (64 + 32ull * ns + 15) & ~15ull;
+    if (pay0 > len) return fail(HFE_ERR_BAD_BLOB, "blob: section directory runs past the end");
+    if (crc32_zlib(b + pay0, len - pay0) != crc) return fail(HFE_ERR_BAD_BLOB, "blob: checksum mismatch");
+    out->n_features = nf;
+    out->n_members = nm;
+    for (uint32_t i = 0; i < ns; ++i) {
+        const uint8_t* d = b + 64 + 32ull * i;
+        uint32_t kind, member;
+        uint64_t off, nbytes, count;
+        std::memcpy(&kind, d, 4);
+        std::memcpy(&member, d + 4, 4);
+        std::memcpy(&off, d + 8, 8);
+        std::memcpy(&nbytes, d + 16, 8);
+        std::memcpy(&count, d + 24, 8);
+        int es = elem_size(kind);
+        if (es == 0) return fail(HFE_ERR_BAD_BLOB, "blob: unknown section kind");
+        if ((off & 15) || off < pay0 || off > len || nbytes > len - off || count > (1ull << 40) ||
+            nbytes != count * (uint64_t)es)
+            return fail(HFE_ERR_BAD_BLOB, "blob: section out of bounds or mis-sized");
+        if (out->sections.count({kind, member})) return fail(HFE_ERR_BAD_BLOB, "blob: duplicate section");
+        out->sections[{kind, member}] = Section{b + off, count};
+    }
+    return HFE_OK;
+}
+
+inline bool all_finite(const double* p, uint64_t n) {
+    for (uint64_t i = 0; i < n; ++i)
+        if (!std::isfinite(p[i])) return false;
+    return true;
+}
+
+// largest float32 <= v  (so that x32 <= result  <=>  (double)x32 <= v)
+inline float floor_to_f32(double v) {
+    float f = (float)v;
+    if ((double)f > v) f = std::nextafterf(f, -INFINITY);
+    return f;
+}
+
+template <typename T>
+inline int upload(Model* m, const std::vector<T>& host, const T** dev) {
+    void* p = nullptr;
+    size_t bytes = std::max<size_t>(host.size() * sizeof(T), 16);
+    HFE_CUDA_TRY(cudaMalloc(&p, bytes));
+    m->allocations.push_back(p);
+    m->device_bytes += bytes;
+    if (!host.empty()) HFE_CUDA_TRY(cudaMemcpy(p, host.data(), host.size() * sizeof(T), cudaMemcpyHostToDevice));
+    *dev = static_cast<const T*>(p);
+    return HFE_OK;
+}
+
+// ---- SVC member --------------------------------------------------------------------------------------------------------
+
+inline int build_svc(Model* m, const ParsedBlob& pb, uint32_t idx) {
+    const Section* ps = pb.find(K_SVC_PARAMS, idx, 8);
+    if (!ps) return fail(HFE_ERR_BAD_BLOB, "blob: SVC params missing");
+    const double* p = ps->f64();
+    if (!all_finite(p, 8)) return fail(HFE_ERR_BAD_BLOB, "blob: non-finite SVC parameter");
+    double n_sv_d = p[4];
+    if (!(n_sv_d >= 1 && n_sv_d <= 1e6) || n_sv_d != std::floor(n_sv_d))
+        return fail(HFE_ERR_BAD_BLOB, "blob: bad support vector count");
+    int n_sv = (int)n_sv_d;
+    // the consistency check scikit-learn applies before handing arrays to libsvm (SK/svm/_base.py:680-686)
+    if (p[5] < 0 || p[6] < 0 || p[5] + p[6] != n_sv_d)
+        return fail(HFE_ERR_BAD_BLOB, "blob: SVC n_support does not add up to the support vector count");
+    const Section* mean = pb.find(K_SVC_MEAN, idx, F);
+    const Section* scale = pb.find(K_SVC_SCALE, idx, F);
+    const Section* sv = pb.find(K_SVC_SV, idx, (uint64_t)n_sv * F);
+    const Section* dual = pb.find(K_SVC_DUAL, idx, n_sv);
+    if (!mean || !scale || !sv || !dual) return fail(HFE_ERR_BAD_BLOB, "blob: SVC section missing or mis-sized");
+    if (!all_finite(mean->f64(), F) || !all_finite(scale->f64(), F) || !all_finite(sv->f64(), (uint64_t)n_sv * F) ||
+        !all_finite(dual->f64(), n_sv))
+        return fail(HFE_ERR_BAD_BLOB, "blob: non-finite SVC table entry");
+    double gamma = p[0];
+    if (!(gamma > 0)) return fail(HFE_ERR_BAD_BLOB, "blob: gamma must be positive");
+    ScoreParams& P = m->base;
+    for (int d = 0; d < F; ++d) {
+        if (scale->f64()[d] == 0.0) return fail(HFE_ERR_BAD_BLOB, "blob: scaler scale_ holds a zero");
+        P.mean[d] = mean->f64()[d];
+        P.scale[d] = scale->f64()[d];
+        P.inv_scale[d] = 1.0 / scale->f64()[d];
+    }
+    P.gamma = gamma;
+    P.c_log2 = gamma * 1.4426950408889634074;
+    P.svc_intercept = p[1];
+    P.prob_a = p[2];
+    P.prob_b = p[3];
+    P.n_sv = n_sv;
+    m->n_sv = n_sv;
+
+    // alternate signs so the running coefficient sum hovers around zero
+    const double* coef = dual->f64();
+    std::vector<int> pos, neg, order;
+    for (int j = 0; j < n_sv; ++j) (coef[j] > 0 ? pos : neg).push_back(j);
+    double run = 0;
+    size_t ip = 0, in = 0;
+    while (ip < pos.size() || in < neg.size()) {
+        int j;
+        if ((run <= 0 && ip < pos.size()) || in >= neg.size()) j = pos[ip++];
+        else j = neg[in++];
+        run += coef[j];
+        order.push_back(j);
+    }
+    int padded = ((n_sv + SV_CHUNK - 1) / SV_CHUNK) * SV_CHUNK;
+    int n_groups = padded / SV_GROUP;
+    std::vector<float4> tab((size_t)n_groups * SV_ROWS, make_float4(0.f, 0.f, 0.f, 0.f));
+    double max_norm = 0, coef_l2 = 0;
+    for (int k = 0; k < n_sv; ++k) {
+        int j = order[k];
+        const double* s = sv->f64() + (size_t)j * F;
+        double ss = 0;
+        for (int d = 0; d < F; ++d) ss += s[d] * s[d];
+        max_norm = std::max(max_norm, std::sqrt(ss));
+        coef_l2 += coef[j] * coef[j];
+        float* base = reinterpret_cast<float*>(&tab[(size_t)(k / SV_GROUP) * SV_ROWS]);
+        int lane = k % SV_GROUP;
+        for (int d = 0; d < F; ++d) base[d * 4 + lane] = (float)(2.0 * P.c_log2 * s[d]);
+        base[F * 4 + lane] = (float)(coef[j] * std::exp2(-P.c_log2 * ss));
+    }
+    // float32 2^x must not overflow: 2c|z||s| <= 100  =>  c|z|^2 <= c*(100/(2c*max|s|))^2
+    double zmax = 100.0 / (2.0 * P.c_log2 * std::max(max_norm, 1e-30));
+    P.zz_limit = std::min(P.c_log2 * zmax * zmax, 900.0);
+    // assumed uncertainty of the float32 decision value (DESIGN.md "error budget"): ~20 sigma of the measured error
+    m->svc_guard = 3.5e-7 * std::sqrt(coef_l2) + 1e-7;
+    P.n_groups = n_groups;
+    std::vector<double> sv_host(sv->f64(), sv->f64() + (size_t)n_sv * F), dual_host(coef, coef + n_sv);
+    int rc;
+    if ((rc = upload(m, tab, &P.sv_tab))) return rc;
+    if ((rc = upload(m, sv_host, &P.sv64))) return rc;
+    if ((rc = upload(m, dual_host, &P.dual64))) return rc;
+    return HFE_OK;
+}
+
+// ---- boosted trees -----------------------------------------------------------------------------------------------------
+
+inline int build_gbt(Model* m, const ParsedBlob& pb, uint32_t idx) {
+    const Section* ps = pb.find(K_GBT_PARAMS, idx, 4);
+    if (!ps || !all_finite(ps->f64(), 4)) return fail(HFE_ERR_BAD_BLOB, "blob: boosting params missing");
+    const double* p = ps->f64();
+    double init_raw = p[0], lr = p[1];
+    if (!(p[2] >= 1 && p[2] <= 1e6 && p[3] >= 1 && p[3] < 2147483648.0))
+        return fail(HFE_ERR_BAD_BLOB, "blob: bad tree counts");
+    int n_trees = (int)p[2];
+    int64_t n_nodes = (int64_t)p[3];
+    const Section* offs = pb.find(K_GBT_OFFSETS, idx, (uint64_t)n_trees + 1);
+    const Section* feat = pb.find(K_GBT_FEATURE, idx, n_nodes);
+    const Section* left = pb.find(K_GBT_LEFT, idx, n_nodes);
+    const Section* right = pb.find(K_GBT_RIGHT, idx, n_nodes);
+    const Section* thr = pb.find(K_GBT_THRESHOLD, idx, n_nodes);
+    const Section* val = pb.find(K_GBT_VALUE, idx, n_nodes);
+    if (!offs || !feat || !left || !right || !thr || !val)
+        return fail(HFE_ERR_BAD_BLOB, "blob: boosting section missing or mis-sized");
+    const uint32_t* off = offs->u32();
+    if (off[0] != 0 || off[n_trees] != (uint64_t)n_nodes) return fail(HFE_ERR_BAD_BLOB, "blob: bad tree offsets");
+
+    std::vector<uint2> nodes((size_t)n_nodes);
+    std::vector<float> value32((size_t)n_nodes);
+    std::vector<double> value64((size_t)n_nodes);
+    std::vector<unsigned short> sk_id((size_t)n_nodes);
+    std::vector<int> tree_off(n_trees + 1);
+    std::vector<unsigned char> depth(n_trees);
+    bool all_stumps = true;
+    int max_depth = 0;
+    struct Split { int f; float thr; };
+    std::map<std::pair<int, uint32_t>, double> merged;   // (feature, thr32 bits) -> sum lr*(vL - vR)
+    double right_sum = 0, sum_max_abs = 0;
+    std::vector<int> newpos, queue, dep;
+    for (int t = 0; t < n_trees; ++t) {
+        if (off[t + 1] <= off[t]) return fail(HFE_ERR_BAD_BLOB, "blob: empty tree");
+        int base = (int)off[t], cnt = (int)(off[t + 1] - off[t]);
+        if (cnt > 65535) return fail(HFE_ERR_UNSUPPORTED, "tree with more than 65535 nodes");
+        tree_off[t] = base;
+        const int32_t* L = left->i32() + base;
+        const int32_t* R = right->i32() + base;
+        const int32_t* Fe = feat->i32() + base;
+        const double* T = thr->f64() + base;
+        const double* V = val->f64() + base;
+        // validate topology: children strictly after parent, in range, each node reached at most once
+        std::vector<char> seen(cnt, 0);
+        seen[0] = 1;
+        for (int i = 0; i < cnt; ++i) {
+            bool leaf = (L[i] == -1);
+            if (leaf != (R[i] == -1)) return fail(HFE_ERR_BAD_BLOB, "blob: half-leaf tree node");
+            if (!std::isfinite(V[i])) return fail(HFE_ERR_BAD_BLOB, "blob: non-finite leaf value");
+            if (leaf) continue;
+            if (L[i] <= i || R[i] <= i || L[i] >= cnt || R[i] >= cnt || L[i] == R[i])
+                return fail(HFE_ERR_BAD_BLOB, "blob: tree child index out of order or range");
+            if (seen[L[i]] || seen[R[i]]) return fail(HFE_ERR_BAD_BLOB, "blob: tree node has two parents");
+            seen[L[i]] = seen[R[i]] = 1;
+            if (Fe[i] < 0 || Fe[i] >= F) return fail(HFE_ERR_BAD_BLOB, "blob: split feature out of range");
+            if (!std::isfinite(T[i])) return fail(HFE_ERR_BAD_BLOB, "blob: non-finite threshold");
+        }
+        for (int i = 0; i < cnt; ++i)
+            if (!seen[i]) return fail(HFE_ERR_BAD_BLOB, "blob: unreachable tree node");
+        // breadth-first re-layout, siblings adjacent
+        newpos.assign(cnt, -1);
+        queue.clear();
+        dep.assign(cnt, 0);
+        queue.push_back(0);
+        newpos[0] = 0;
+        int next_free = 1, tdepth = 0;
+        for (size_t qi = 0; qi < queue.size(); ++qi) {
+            int i = queue[qi];
+            if (L[i] == -1) continue;
+            newpos[L[i]] = next_free++;
+            newpos[R[i]] = next_free++;
+            dep[L[i]] = dep[R[i]] = dep[i] + 1;
+            tdepth = std::max(tdepth, dep[i] + 1);
+            queue.push_back(L[i]);
+            queue.push_back(R[i]);
+        }
+        if (tdepth > 255) return fail(HFE_ERR_UNSUPPORTED, "tree deeper than 255 levels");
+        depth[t] = (unsigned char)tdepth;
+        max_depth = std::max(max_depth, tdepth);
+        double tree_max = 0;
+        for (int i = 0; i < cnt; ++i) tree_max = std::max(tree_max, std::fabs(lr * V[i]));
+        sum_max_abs += tree_max;
+        for (int i = 0; i < cnt; ++i) {
+            int q = base + newpos[i];
+            sk_id[q] = (unsigned short)i;
+            value64[q] = lr * V[i];
+            value32[q] = (float)value64[q];
+            if (L[i] == -1) {
+                float inf = INFINITY;
+                uint32_t bits;
+                std::memcpy(&bits, &inf, 4);
+                nodes[q] = make_uint2(bits, (uint32_t)newpos[i]);    // self loop: x > +inf is never true
+            } else {
+                float t32 = floor_to_f32(T[i]);
+                uint32_t bits;
+                std::memcpy(&bits, &t32, 4);
+                nodes[q] = make_uint2(bits, ((uint32_t)Fe[i] << 24) | (uint32_t)newpos[L[i]]);
+            }
+        }
+        bool stump = (cnt == 3 && L[0] != -1 && L[L[0]] == -1 && L[R[0]] == -1);
+        all_stumps = all_stumps && stump;
+        if (stump) {
+            float t32 = floor_to_f32(T[0]);
+            uint32_t bits;
+            std::memcpy(&bits, &t32, 4);
+            merged[{Fe[0], bits}] += lr * V[L[0]] - lr * V[R[0]];
+            right_sum += lr * V[R[0]];
+        }
+    }
+    tree_off[n_trees] = (int)n_nodes;
+    ScoreParams& P = m->base;
+    P.n_trees = n_trees;
+    P.gbt_init = init_raw;
+    m->n_trees = n_trees;
+    m->n_nodes = (int)n_nodes;
+    m->max_depth = max_depth;
+    m->gbt_guard = 2.4e-7 * sum_max_abs + 1e-9;       // float32 leaf values and float32 partial sums
+    if (all_stumps && (int)merged.size() <= MAX_SPLITS) {
+        m->tree_mode = 1;
+        int s = 0, f_cur = 0;
+        P.split_begin[0] = 0;
+        for (auto& kv : merged) {               // std::map iterates sorted by (feature, bits)
+            while (f_cur < kv.first.first) P.split_begin[++f_cur] = s;
+            float t32;
+            std::memcpy(&t32, &kv.first.second, 4);
+            P.split_thr[s] = t32;
+            P.split_delta[s] = (float)kv.second;
+            ++s;
+        }
+        while (f_cur < F) P.split_begin[++f_cur] = s;
+        P.n_splits = s;
+        P.gbt_split_base = init_raw + right_sum;
+        m->n_splits = s;
+    } else {
+        m->tree_mode = 2;
+    }
+    int rc;
+    if ((rc = upload(m, nodes, &P.nodes))) return rc;
+    if ((rc = upload(m, value32, &P.value32))) return rc;
+    if ((rc = upload(m, value64, &P.value64))) return rc;
+    if ((rc = upload(m, tree_off, &P.tree_off))) return rc;
+    if ((rc = upload(m, depth, &P.tree_depth))) return rc;
+    if ((rc = upload(m, sk_id, &P.sk_id))) return rc;
+    return HFE_OK;
+}
+
+inline int build_model(const uint8_t* blob, size_t len, int device, Model** out) {
+    ParsedBlob pb;
+    int rc = parse_blob(blob, len, &pb);
+    if (rc) return rc;
+    if (pb.n_features != (uint32_t)F)
+        return fail(HFE_ERR_UNSUPPORTED, "this build scores the 17-feature schema only (HFE_N_FEATURES)");
+    if (pb.n_members > (uint32_t)MAX_MEMBERS) return fail(HFE_ERR_UNSUPPORTED, "more than 4 stack members");
+    const Section* fin = pb.find(K_FINAL, STACK_LEVEL, pb.n_members + 1);
+    const Section* cls = pb.find(K_CLASSES, STACK_LEVEL, 2);
+    if (!fin || !cls || !all_finite(fin->f64(), pb.n_members + 1))
+        return fail(HFE_ERR_BAD_BLOB, "blob: combiner section missing or non-finite");
+    HFE_CUDA_TRY(cudaSetDevice(device));
+    Model* m = new Model();
+    m->device = device;
+    m->n_members = (int)pb.n_members;
+    ScoreParams& P = m->base;
+    std::memset(&P, 0, sizeof(P));
+    P.slot_svc = P.slot_gbt = P.slot_lin = -1;
+    P.n_members = m->n_members;
+    P.perm_col = -1;
+    for (uint32_t i = 0; i < pb.n_members && rc == HFE_OK; ++i) {
+        P.final_coef[i] = fin->f64()[i];
+        if (pb.has(K_SVC_PARAMS, i)) {
+            if (P.slot_svc >= 0) rc = fail(HFE_ERR_UNSUPPORTED, "more than one SVC member");
+            else { P.slot_svc = (int)i; m->kinds[i] = KIND_SVC; rc = build_svc(m, pb, i); }
+        } else if (pb.has(K_GBT_PARAMS, i)) {
+            if (P.slot_gbt >= 0) rc = fail(HFE_ERR_UNSUPPORTED, "more than one boosting member");
+            else { P.slot_gbt = (int)i; m->kinds[i] = KIND_GBT; rc = build_gbt(m, pb, i); }
+        } else if (pb.has(K_LIN_PARAMS, i)) {
+            const Section* lp = pb.find(K_LIN_PARAMS, i, F + 1);
+            if (P.slot_lin >= 0) rc = fail(HFE_ERR_UNSUPPORTED, "more than one logistic member");
+            else if (!lp || !all_finite(lp->f64(), F + 1)) rc = fail(HFE_ERR_BAD_BLOB, "blob: logistic params bad");
+            else {
+                P.slot_lin = (int)i;
+                m->kinds[i] = KIND_LIN;
+                for (int d = 0; d < F; ++d) P.lin_coef[d] = lp->f64()[d];
+                P.lin_intercept = lp->f64()[F];
+            }
+        } else {
+            rc = fail(HFE_ERR_BAD_BLOB, "blob: member without parameter section");
+        }
+    }
+    if (rc == HFE_OK) {
+        P.final_intercept = fin->f64()[pb.n_members];
+        // guard bands: how far the float32 decision value may be off, pushed through the Platt slope
+        double slope = std::fabs(P.prob_a) * 0.25;                       // |d r / d f| <= |A|/4
+        P.solver_guard = std::fabs(P.prob_a) * m->svc_guard;             // in units of t = f*A + B
+        if (P.slot_svc >= 0) {
+            std::vector<double> edges = find_solver_edges();
+            if (edges.size() > (size_t)MAX_EDGES) rc = fail(HFE_ERR_UNSUPPORTED, "coupling solver has too many edges");
+            else {
+                P.n_edges = (int)edges.size();
+                for (size_t e = 0; e < edges.size(); ++e) P.edges[e] = edges[e];
+            }
+        }
+        double w_svc = P.slot_svc >= 0 ? std::fabs(P.final_coef[P.slot_svc]) : 0.0;
+        P.label_guard = 2.0 * w_svc * slope * m->svc_guard + 1e-9 +
+                        (P.slot_gbt >= 0 ? std::fabs(P.final_coef[P.slot_gbt]) * 0.25 * m->gbt_guard : 0.0);
+    }
+    if (rc != HFE_OK) {
+        for (void* p : m->allocations) cudaFree(p);
+        delete m;
+        return rc;
+    }
+    *out = m;
+    return HFE_OK;
+}
+
+}  // namespace hfe

@@ -1,0 +1,254 @@
+"""Host-side mirror of the reference's model object: the scikit-learn estimator protocol over the CUDA scorer.
+
+``predict_hf.py:36`` and ``train_ensemble_public.py:62`` call ``clf.predict_proba(X)`` on an unpickled
+``StackingClassifier``.  ``HFStackB200`` is the object those lines get instead: same method names, argument meaning,
+return types (float64 ``[n,2]`` ordered as ``classes_``; ``predict`` -> float64 labels decided by the combiner's strict
+``z > 0``, SK/linear_model/_base.py:398-425) and the same ``ValueError`` behaviour for malformed input
+(1-D input, wrong width, empty, NaN/Inf -- SK/svm/_base.py:648-660).  Everything numeric happens in ``libhfe.so``;
+there is no CPU path.
+
+numpy entry points go through ``hfe_predict_host`` (H2D copy -> device ingest/transpose -> fused kernel -> D2H).  The
+``*_device`` methods take a column-major float32 CUDA tensor ``[17, ld]`` (torch is used for device memory and
+streams only) and enqueue on the current stream without synchronising.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import capi
+from .export import ModelArrays, arrays_from_published_pickle, arrays_from_stack, read_blob, write_blob
+from .schema import N_FEATURES
+
+
+def _validate_X(X, n_features):
+    """The checks scikit-learn's ``validate_data`` applies on this path, with its messages."""
+    arr = np.asarray(X)
+    if arr.dtype == object or arr.dtype.kind in "USV":
+        arr = arr.astype(np.float64)                      # raises ValueError for non-numeric content, like sklearn
+    if arr.dtype.kind == "c":
+        raise ValueError(f"Complex data not supported\n{arr}\n")
+    if arr.ndim == 0:
+        raise ValueError(f"Expected 2D array, got scalar array instead:\narray={arr!r}.")
+    if arr.ndim == 1:
+        raise ValueError(f"Expected 2D array, got 1D array instead:\narray={arr!r}.\nReshape your data either using "
+                         "array.reshape(-1, 1) if your data has a single feature or array.reshape(1, -1) if it "
+                         "contains a single sample.")
+    if arr.ndim > 2:
+        raise ValueError(f"Found array with dim {arr.ndim}, while dim <= 2 is required.")
+    if arr.shape[0] == 0:
+        raise ValueError(f"Found array with 0 sample(s) (shape={arr.shape}) while a minimum of 1 is required.")
+    if arr.shape[1] != n_features:
+        raise ValueError(f"X has {arr.shape[1]} features, but HFStackB200 is expecting {n_features} features as "
+                         "input.")
+    arr = np.ascontiguousarray(arr, dtype=np.float64)
+    if not np.isfinite(arr).all():
+        if np.isnan(arr).any():
+            raise ValueError("Input X contains NaN.")
+        raise ValueError("Input X contains infinity or a value too large for dtype('float64').")
+    return arr
+
+
+class HFStackB200:
+    """Drop-in for the fitted ``StackingClassifier`` of train_ensemble_public.py:43-48 on one B200."""
+
+    def __init__(self, blob: bytes, device: int = 0, arrays: ModelArrays | None = None):
+        self._lib = capi.load_library()
+        self._blob = bytes(blob)
+        self._arrays = arrays if arrays is not None else read_blob(self._blob)
+        self.device = int(device)
+        handle = C.c_void_p()
+        capi.check(self._lib.hfe_model_create(self._blob, len(self._blob), self.device, C.byref(handle)))
+        self._handle = handle
+        self.classes_ = np.array(self._arrays.classes, dtype=np.float64)
+        self.n_features_in_ = N_FEATURES
+        info = capi.ModelInfo()
+        capi.check(self._lib.hfe_model_get_info(self._handle, C.byref(info)))
+        self.info = info
+        self.n_members = int(info.n_members)
+        self.last_status = None
+
+    # -- constructors ----------------------------------------------------------------------------------------------
+    @classmethod
+    def from_arrays(cls, arrays: ModelArrays, device: int = 0):
+        return cls(write_blob(arrays), device=device, arrays=arrays)
+
+    @classmethod
+    def from_sklearn(cls, stack, device: int = 0):
+        """Walk a live fitted StackingClassifier (attributes only) -- replaces pickling it."""
+        return cls.from_arrays(arrays_from_stack(stack, source="live sklearn object"), device=device)
+
+    @classmethod
+    def from_published_pickle(cls, path, device: int = 0):
+        """Statically decode the reference's hf_predict_model.pkl (never unpickled) -- replaces predict_hf.py:33-34."""
+        return cls.from_arrays(arrays_from_published_pickle(path), device=device)
+
+    @classmethod
+    def from_blob_file(cls, path, device: int = 0):
+        with open(path, "rb") as fh:
+            return cls(fh.read(), device=device)
+
+    def close(self):
+        if getattr(self, "_handle", None) is not None and self._handle:
+            self._lib.hfe_model_destroy(self._handle)
+            self._handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- numpy (host) protocol -------------------------------------------------------------------------------------
+    def _host_call(self, X, want_labels=False, want_decision=False, want_meta=False):
+        arr = _validate_X(X, self.n_features_in_)
+        n = arr.shape[0]
+        proba = np.empty((n, 2), dtype=np.float64)
+        labels = np.empty(n, dtype=np.uint8) if want_labels else None
+        decision = np.empty(n, dtype=np.float64) if want_decision else None
+        meta = np.empty((n, self.n_members), dtype=np.float64) if want_meta else None
+
+        def ptr(a):
+            return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+        code = self._lib.hfe_predict_host(self._handle, ptr(arr), n, ptr(proba), ptr(labels), ptr(decision),
+                                          ptr(meta))
+        if code == capi.HFE_ERR_NONFINITE_INPUT:
+            raise ValueError("Input X contains infinity or a value too large for dtype('float32').")
+        capi.check(code)
+        return proba, labels, decision, meta
+
+    def predict_proba(self, X):
+        """``[n,2]`` float64, columns ordered as ``classes_`` (predict_hf.py:36; train_ensemble_public.py:62)."""
+        return self._host_call(X)[0]
+
+    def predict(self, X):
+        """``classes_[z > 0]`` (SK/ensemble/_stacking.py:711-766)."""
+        return self.classes_[self._host_call(X, want_labels=True)[1].astype(np.int64)]
+
+    def decision_function(self, X):
+        return self._host_call(X, want_decision=True)[2]
+
+    def transform(self, X):
+        """Member P(class 1) columns ``[n, n_members]`` (SK/ensemble/_stacking.py:814-830)."""
+        return self._host_call(X, want_meta=True)[3]
+
+    def predict_log_proba(self, X):
+        return np.log(self.predict_proba(X))
+
+    def score(self, X, y):
+        """Mean accuracy, the default scorer permutation importance uses (ClassifierMixin.score)."""
+        return float(np.mean(self.predict(X) == np.asarray(y)))
+
+    def apply(self, X):
+        """Leaf ids of the boosting member ``[n, n_trees]`` (GradientBoostingClassifier.apply, ids as integers)."""
+        import torch
+
+        arr = _validate_X(X, self.n_features_in_)
+        x = self.to_device_colmajor(arr)
+        n = arr.shape[0]
+        leaves = torch.empty((n, int(self.info.n_trees)), dtype=torch.int16, device=x.device)
+        capi.check(self._lib.hfe_apply(self._handle, x.data_ptr(), n, x.shape[1], leaves.data_ptr(), self._stream()))
+        return leaves.cpu().numpy().view(np.uint16).astype(np.int64)
+
+    # -- device-native protocol (timed path) ---------------------------------------------------------------------------
+    def _stream(self):
+        import torch
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def to_device_colmajor(self, X):
+        """Row-major host array -> column-major float32 CUDA tensor ``[17, ld]`` via the device ingest kernel."""
+        import torch
+
+        arr = np.ascontiguousarray(X, dtype=np.float64)
+        n = arr.shape[0]
+        ld = (n + 3) & ~3
+        with torch.cuda.device(self.device):
+            src = torch.from_numpy(arr).to(f"cuda:{self.device}")
+            dst = torch.zeros((self.n_features_in_, ld), dtype=torch.float32, device=src.device)
+            status = torch.zeros(capi.STATUS_WORDS, dtype=torch.int32, device=src.device)
+            capi.check(self._lib.hfe_ingest_rowmajor_f64(src.data_ptr(), n, self.n_features_in_, dst.data_ptr(), ld,
+                                                         status.data_ptr(), self._stream()))
+        return dst
+
+    def new_status(self):
+        import torch
+        return torch.zeros(capi.STATUS_WORDS, dtype=torch.int32, device=f"cuda:{self.device}")
+
+    def predict_proba_device(self, x, n=None, out=None, status=None):
+        """Enqueue the fused kernel on the current stream.  ``x``: float32 CUDA tensor ``[17, ld]`` (column-major
+        feature matrix); returns the float32 ``[n,2]`` output tensor.  Does not synchronise."""
+        import torch
+
+        n = x.shape[1] if n is None else int(n)
+        if out is None:
+            out = torch.empty((n, 2), dtype=torch.float32, device=x.device)
+        if status is None:
+            status = self.new_status()
+        capi.check(self._lib.hfe_predict_proba(self._handle, x.data_ptr(), n, x.stride(0), out.data_ptr(),
+                                               status.data_ptr(), self._stream()))
+        self.last_status = status
+        return out
+
+    def score_device(self, x, n=None, perm_col=-1, perm_idx=None, out=None, labels=None, decision=None, meta=None,
+                     y=None, score=None, status=None):
+        """``hfe_score``: any subset of outputs; optional permuted column and on-device accuracy count."""
+        n = x.shape[1] if n is None else int(n)
+        if status is None:
+            status = self.new_status()
+
+        def p(t):
+            return t.data_ptr() if t is not None else None
+
+        capi.check(self._lib.hfe_score(self._handle, x.data_ptr(), n, x.stride(0), int(perm_col), p(perm_idx), p(out),
+                                       p(labels), p(decision), p(meta), p(y), p(score), status.data_ptr(),
+                                       self._stream()))
+        self.last_status = status
+        return status
+
+    def predict_proba_f64_device(self, x, n=None, out=None, status=None):
+        """Every row through the float64 path (calibration aid)."""
+        import torch
+
+        n = x.shape[1] if n is None else int(n)
+        if out is None:
+            out = torch.empty((n, 2), dtype=torch.float64, device=x.device)
+        if status is None:
+            status = self.new_status()
+        capi.check(self._lib.hfe_predict_proba_f64(self._handle, x.data_ptr(), n, x.stride(0), out.data_ptr(),
+                                                   status.data_ptr(), self._stream()))
+        return out
+
+    def apply_device(self, x, n=None):
+        import torch
+
+        n = x.shape[1] if n is None else int(n)
+        leaves = torch.empty((n, int(self.info.n_trees)), dtype=torch.int16, device=x.device)
+        capi.check(self._lib.hfe_apply(self._handle, x.data_ptr(), n, x.stride(0), leaves.data_ptr(), self._stream()))
+        return leaves
+
+
+def synth_rows_device(specs, seed, row0, n, device=0, out=None):
+    """Column-major float32 ``[len(specs), ld]`` synthetic rows generated on the device (``hfe_synth_rows``)."""
+    import torch
+
+    from .synth import pack_specs
+
+    lib = capi.load_library()
+    col_id, base, step, off, thr = pack_specs(specs)
+    dev = f"cuda:{device}"
+    ld = (n + 3) & ~3
+    with torch.cuda.device(device):
+        t_col = torch.from_numpy(col_id).to(dev)
+        t_base = torch.from_numpy(base).to(dev)
+        t_step = torch.from_numpy(step).to(dev)
+        t_off = torch.from_numpy(off).to(dev)
+        t_thr = torch.from_numpy(thr.view(np.int32)).to(dev)
+        if out is None:
+            out = torch.zeros((len(specs), ld), dtype=torch.float32, device=dev)
+        capi.check(lib.hfe_synth_rows(int(seed), int(row0), int(n), len(specs), t_col.data_ptr(), t_base.data_ptr(),
+                                      t_step.data_ptr(), t_off.data_ptr(), t_thr.data_ptr(), out.data_ptr(),
+                                      out.stride(0), torch.cuda.current_stream(device).cuda_stream))
+        torch.cuda.current_stream(device).synchronize()     # the table tensors above must outlive the kernel
+    return out
