@@ -111,6 +111,9 @@ int hfe_synth_rows(uint64_t seed, int64_t row0, int64_t n, int32_t n_cols, const
  * column-major float32 with round-to-nearest, the cast SK/ensemble/_gb.py:1579-1604 applies; sets HFE_ROW_NONFINITE. */
 int hfe_ingest_rowmajor_f64(const double* x_rowmajor, int64_t n, int32_t n_features, float* x, int64_t ld,
                             uint32_t* status, void* stream);
+/* Same for a row-major float32 matrix (a cohort already held in single precision): transpose only. */
+int hfe_ingest_rowmajor_f32(const float* x_rowmajor, int64_t n, int32_t n_features, float* x, int64_t ld,
+                            uint32_t* status, void* stream);
 
 /* Host-buffer convenience used by the facade for numpy inputs: copies X (row-major float64, host) to the device,
  * ingests, scores, copies P back (float64 [n,2]; p0 = 1 - p1) and synchronises.  Allocates temporaries.

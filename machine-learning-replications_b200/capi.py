@@ -16,7 +16,7 @@ ROW_NONFINITE = 1
 EXPORTS = [
     "hfe_abi_version", "hfe_last_error_string", "hfe_model_create", "hfe_model_destroy", "hfe_model_get_info",
     "hfe_predict_proba", "hfe_predict", "hfe_score", "hfe_apply", "hfe_predict_proba_f64", "hfe_synth_rows",
-    "hfe_ingest_rowmajor_f64", "hfe_predict_host",
+    "hfe_ingest_rowmajor_f64", "hfe_ingest_rowmajor_f32", "hfe_predict_host",
 ]
 
 
@@ -62,6 +62,7 @@ def load_library(path: str = LIB_PATH):
     lib.hfe_predict_proba_f64.argtypes = [vp, vp, i64, i64, vp, vp, vp]
     lib.hfe_synth_rows.argtypes = [u64, i64, i64, i32, vp, vp, vp, vp, vp, vp, i64, vp]
     lib.hfe_ingest_rowmajor_f64.argtypes = [vp, i64, i32, vp, i64, vp, vp]
+    lib.hfe_ingest_rowmajor_f32.argtypes = [vp, i64, i32, vp, i64, vp, vp]
     lib.hfe_predict_host.argtypes = [vp, vp, i64, vp, vp, vp, vp]
     for name in EXPORTS:
         fn = getattr(lib, name)

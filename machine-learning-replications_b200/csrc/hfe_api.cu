@@ -30,8 +30,8 @@ int launch_score(const Model* m, const ScoreParams& P, cudaStream_t stream) {
     size_t sv_bytes = 0;
     int smem_groups = 0;
     if (SVC) {
-        smem_groups = std::min(P.n_groups, TM == 2 ? 256 : MAX_SMEM_GROUPS);
-        sv_bytes = (size_t)smem_groups * SV_ROWS * sizeof(float4);
+        smem_groups = std::min(P.n_groups, TM == 2 ? 64 : MAX_SMEM_GROUPS);
+        sv_bytes = ((size_t)smem_groups * SV_ROWS + SV_PAD_ROWS) * sizeof(float4);
     }
     size_t smem = sv_bytes + (TM == 2 ? (size_t)F * BLOCK_ROWS * sizeof(float) : 0);
     auto kernel = hfe_score_kernel<SVC, TM>;
@@ -39,7 +39,7 @@ int launch_score(const Model* m, const ScoreParams& P, cudaStream_t stream) {
     static cudaError_t attr_err[16];
     int dev = m->device & 15;
     std::call_once(once[dev], [&] {
-        attr_err[dev] = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        attr_err[dev] = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024);
     });
     if (attr_err[dev] != cudaSuccess)
         return fail(HFE_ERR_CUDA, std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(attr_err[dev]));
@@ -70,6 +70,8 @@ int score_common(const hfe_model* model, const float* x, int64_t n, int64_t ld, 
     if (perm_col >= F || (perm_col >= 0 && !perm_idx))
         return fail(HFE_ERR_INVALID_ARGUMENT, "bad permutation column / index array");
     if ((y != nullptr) != (score != nullptr)) return fail(HFE_ERR_INVALID_ARGUMENT, "y and score go together");
+    if (reinterpret_cast<uintptr_t>(out) & 15)
+        return fail(HFE_ERR_INVALID_ARGUMENT, "probability output must be 16-byte aligned");
     const Model* m = model->impl;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     HFE_CUDA_TRY(cudaSetDevice(m->device));
@@ -98,6 +100,25 @@ int score_common(const hfe_model* model, const float* x, int64_t n, int64_t ld, 
     return dispatch_score(m, P, s);
 }
 
+}  // namespace
+
+namespace {
+template <typename T>
+int ingest_common(const T* x_rowmajor, int64_t n, int32_t n_features, float* x, int64_t ld, uint32_t* status,
+                  void* stream) {
+    if (n < 0 || n_features < 1 || n_features > 64 || ld < n)
+        return fail(HFE_ERR_INVALID_ARGUMENT, "bad ingest sizes");
+    if (!status) return fail(HFE_ERR_INVALID_ARGUMENT, "null status array");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    HFE_CUDA_TRY(cudaMemsetAsync(status, 0, HFE_STATUS_WORDS * sizeof(uint32_t), s));
+    if (n == 0) return HFE_OK;
+    if (!x_rowmajor || !x) return fail(HFE_ERR_INVALID_ARGUMENT, "null ingest buffer");
+    long long blocks = (n + BLOCK_THREADS - 1) / BLOCK_THREADS;
+    size_t smem = (size_t)BLOCK_THREADS * (n_features + 1) * sizeof(float);
+    hfe_ingest_kernel<T><<<(unsigned)blocks, BLOCK_THREADS, smem, s>>>(x_rowmajor, n, n_features, x, ld, status);
+    HFE_CUDA_TRY(cudaGetLastError());
+    return HFE_OK;
+}
 }  // namespace
 
 extern "C" {
@@ -213,18 +234,12 @@ int hfe_synth_rows(uint64_t seed, int64_t row0, int64_t n, int32_t n_cols, const
 
 int hfe_ingest_rowmajor_f64(const double* x_rowmajor, int64_t n, int32_t n_features, float* x, int64_t ld,
                             uint32_t* status, void* stream) {
-    if (n < 0 || n_features < 1 || n_features > 64 || ld < n)
-        return fail(HFE_ERR_INVALID_ARGUMENT, "bad ingest sizes");
-    if (!status) return fail(HFE_ERR_INVALID_ARGUMENT, "null status array");
-    cudaStream_t s = static_cast<cudaStream_t>(stream);
-    HFE_CUDA_TRY(cudaMemsetAsync(status, 0, HFE_STATUS_WORDS * sizeof(uint32_t), s));
-    if (n == 0) return HFE_OK;
-    if (!x_rowmajor || !x) return fail(HFE_ERR_INVALID_ARGUMENT, "null ingest buffer");
-    long long blocks = (n + BLOCK_THREADS - 1) / BLOCK_THREADS;
-    size_t smem = (size_t)BLOCK_THREADS * (n_features + 1) * sizeof(float);
-    hfe_ingest_kernel<<<(unsigned)blocks, BLOCK_THREADS, smem, s>>>(x_rowmajor, n, n_features, x, ld, status);
-    HFE_CUDA_TRY(cudaGetLastError());
-    return HFE_OK;
+    return ingest_common(x_rowmajor, n, n_features, x, ld, status, stream);
+}
+
+int hfe_ingest_rowmajor_f32(const float* x_rowmajor, int64_t n, int32_t n_features, float* x, int64_t ld,
+                            uint32_t* status, void* stream) {
+    return ingest_common(x_rowmajor, n, n_features, x, ld, status, stream);
 }
 
 int hfe_predict_host(const hfe_model* model, const double* x_rowmajor, int64_t n, double* proba_n2, uint8_t* labels,

@@ -21,7 +21,7 @@ namespace hfe {
 constexpr int BLOCK_THREADS = 256;
 constexpr int ROWS_PER_THREAD = 4;
 constexpr int BLOCK_ROWS = BLOCK_THREADS * ROWS_PER_THREAD;
-constexpr int MAX_SMEM_GROUPS = 640;      // support-vector groups staged per pass (640*18*16 B = 180 KB)
+constexpr int MAX_SMEM_GROUPS = 160;      // support-vector groups staged per pass (160*36*16 B = 90 KB)
 constexpr int TREE_CHUNK = 16;            // float32 partial sums over trees are folded into float64 every 16 trees
 #ifndef HFE_MIN_BLOCKS
 #define HFE_MIN_BLOCKS 2                  // resident blocks per SM the fused kernel is compiled for (register cap)
@@ -81,8 +81,9 @@ __device__ __noinline__ RowResult finish_row(const ScoreParams& P, bool has_svc,
     return r;
 }
 
-__device__ __forceinline__ void store_row(const ScoreParams& P, long long row, const RowResult& r) {
-    if (P.out) {
+__device__ __forceinline__ void store_row(const ScoreParams& P, long long row, const RowResult& r,
+                                          bool write_out = true) {
+    if (P.out && write_out) {
         P.out[2 * row] = (float)(1.0 - r.p1);
         P.out[2 * row + 1] = (float)r.p1;
     }
@@ -196,7 +197,7 @@ __global__ void __launch_bounds__(BLOCK_THREADS, HFE_MIN_BLOCKS)
 hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float4* s_sv = reinterpret_cast<float4*>(smem_raw);                       // [smem_groups][SV_ROWS]
-    float* s_xt = reinterpret_cast<float*>(smem_raw) + (SVC ? (size_t)smem_groups * SV_ROWS * 4 : 0);  // [F][BLOCK_ROWS]
+    float* s_xt = reinterpret_cast<float*>(smem_raw) + (SVC ? ((size_t)smem_groups * SV_ROWS + SV_PAD_ROWS) * 4 : 0);  // [F][BLOCK_ROWS]
     __shared__ double s_x[F], s_z[F], s_red[2 * BLOCK_THREADS / 32];
     __shared__ unsigned int s_nfix, s_nbad, s_hits;
     __shared__ unsigned short s_fix[BLOCK_ROWS];
@@ -283,25 +284,32 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
     }
 
     // ---- logistic member + standardisation (float64), z rounded once to float32 for the RBF sum -----------------------
+    // z2[f][p] packs rows (2p, 2p+1) of feature f into one 64-bit register pair for FFMA2.
     double zl[R], zz[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) { zl[r] = P.lin_intercept; zz[r] = 0.0; }
-    float z[F][R];
+    float2 z2[F][R / 2];
 #pragma unroll
     for (int f = 0; f < F; ++f) {
+        float zf[R];
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             double xd = (double)xv[f][r];
             if (has_lin) zl[r] = fma(xd, P.lin_coef[f], zl[r]);
+            zf[r] = 0.f;
             if (SVC) {
                 double zd = (xd - P.mean[f]) * P.inv_scale[f];
                 zz[r] = fma(zd, zd, zz[r]);
-                z[f][r] = (float)zd;
+                zf[r] = (float)zd;
             }
         }
+#pragma unroll
+        for (int p = 0; p < R / 2; ++p) z2[f][p] = make_float2(zf[2 * p], zf[2 * p + 1]);
     }
 
-    // ---- RBF sum: 4 support vectors x 4 rows per inner tile, table in shared memory ------------------------------------
+    // ---- RBF sum: 4 support vectors x 4 rows per tile, packed FFMA2, table streamed from shared memory ------------------
+    // The table is a linear stream of steps (two float4 each); a 3-deep register ring keeps the LDS.128 two steps
+    // ahead of their first use.
     double acc64[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) acc64[r] = 0.0;
@@ -309,43 +317,56 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
         for (int g0 = 0; g0 < P.n_groups; g0 += smem_groups) {
             int ng = min(smem_groups, P.n_groups - g0);
             __syncthreads();
-            for (int i = tid; i < ng * SV_ROWS; i += BLOCK_THREADS) s_sv[i] = __ldg(P.sv_tab + (size_t)g0 * SV_ROWS + i);
+            for (int i = tid; i < ng * SV_ROWS + SV_PAD_ROWS; i += BLOCK_THREADS)
+                s_sv[i] = (i < ng * SV_ROWS) ? __ldg(P.sv_tab + (size_t)g0 * SV_ROWS + i) : make_float4(0.f, 0.f, 0.f, 0.f);
             __syncthreads();
+            const float4* tab = s_sv;
+            float4 ring_a[3], ring_b[3];
+            ring_a[0] = tab[0]; ring_b[0] = tab[1];
+            ring_a[1] = tab[2]; ring_b[1] = tab[3];
 #pragma unroll 1
             for (int g = 0; g < ng; g += SV_CHUNK / SV_GROUP) {
-                float acc[R];
+                float2 acc2[R / 2];
 #pragma unroll
-                for (int r = 0; r < R; ++r) acc[r] = 0.f;
+                for (int p = 0; p < R / 2; ++p) acc2[p] = make_float2(0.f, 0.f);
 #pragma unroll
                 for (int h = 0; h < SV_CHUNK / SV_GROUP; ++h) {
-                    const float4* tab = s_sv + (g + h) * SV_ROWS;
-                    float t[4][R];
-                    float4 w = tab[0];
+                    float2 t2[SV_GROUP][R / 2];
 #pragma unroll
-                    for (int r = 0; r < R; ++r) {
-                        t[0][r] = z[0][r] * w.x; t[1][r] = z[0][r] * w.y;
-                        t[2][r] = z[0][r] * w.z; t[3][r] = z[0][r] * w.w;
-                    }
+                    for (int st = 0; st < SV_STEPS; ++st) {
+                        // SV_STEPS % 3 == 0, so the ring slot of a step is the same in every group
+                        ring_a[(st + 2) % 3] = tab[2 * (st + 2)];
+                        ring_b[(st + 2) % 3] = tab[2 * (st + 2) + 1];
+                        const float4 a = ring_a[st % 3], b = ring_b[st % 3];
+                        const float2 w[SV_GROUP] = {make_float2(a.x, a.y), make_float2(a.z, a.w),
+                                                    make_float2(b.x, b.y), make_float2(b.z, b.w)};
+                        if (st == 0) {
 #pragma unroll
-                    for (int d = 1; d < F; ++d) {
-                        w = tab[d];
+                            for (int q = 0; q < SV_GROUP; ++q)
 #pragma unroll
-                        for (int r = 0; r < R; ++r) {
-                            t[0][r] = fmaf(z[d][r], w.x, t[0][r]); t[1][r] = fmaf(z[d][r], w.y, t[1][r]);
-                            t[2][r] = fmaf(z[d][r], w.z, t[2][r]); t[3][r] = fmaf(z[d][r], w.w, t[3][r]);
+                                for (int p = 0; p < R / 2; ++p) t2[q][p] = __fmul2_rn(z2[0][p], w[q]);
+                        } else if (st < F) {
+#pragma unroll
+                            for (int q = 0; q < SV_GROUP; ++q)
+#pragma unroll
+                                for (int p = 0; p < R / 2; ++p) t2[q][p] = __ffma2_rn(z2[st][p], w[q], t2[q][p]);
+                        } else {
+#pragma unroll
+                            for (int q = 0; q < SV_GROUP; ++q)
+#pragma unroll
+                                for (int p = 0; p < R / 2; ++p) {
+                                    float2 e = make_float2(ex2_approx(t2[q][p].x), ex2_approx(t2[q][p].y));
+                                    acc2[p] = __ffma2_rn(w[q], e, acc2[p]);
+                                }
                         }
                     }
-                    float4 cf = tab[F];
-#pragma unroll
-                    for (int r = 0; r < R; ++r) {
-                        acc[r] = fmaf(cf.x, ex2_approx(t[0][r]), acc[r]);
-                        acc[r] = fmaf(cf.y, ex2_approx(t[1][r]), acc[r]);
-                        acc[r] = fmaf(cf.z, ex2_approx(t[2][r]), acc[r]);
-                        acc[r] = fmaf(cf.w, ex2_approx(t[3][r]), acc[r]);
-                    }
+                    tab += SV_ROWS;
                 }
 #pragma unroll
-                for (int r = 0; r < R; ++r) acc64[r] += (double)acc[r];
+                for (int p = 0; p < R / 2; ++p) {
+                    acc64[2 * p] += (double)acc2[p].x;
+                    acc64[2 * p + 1] += (double)acc2[p].y;
+                }
             }
         }
     }
@@ -353,9 +374,11 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
     // ---- float64 epilogue: Platt, coupling, links, combiner -------------------------------------------------------------
     unsigned fixmask = 0;
     unsigned char lab[R];
+    float po[2 * R];
 #pragma unroll
     for (int r = 0; r < R; ++r) {
         lab[r] = 0;
+        po[2 * r] = po[2 * r + 1] = 0.f;
         if (row0 + r >= P.n) continue;
         double f_svc = 0.0;
         bool uncertain = false;
@@ -365,9 +388,16 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
             uncertain = !(czz <= P.zz_limit);
         }
         RowResult res = finish_row(P, SVC, TREE_MODE != 0, has_lin, f_svc, raw[r], zl[r]);
-        store_row(P, row0 + r, res);
+        store_row(P, row0 + r, res, !full);
+        po[2 * r] = (float)(1.0 - res.p1);
+        po[2 * r + 1] = (float)res.p1;
         lab[r] = res.z > 0 ? 1 : 0;
         if (res.uncertain || uncertain) fixmask |= 1u << r;
+    }
+    if (P.out && full) {                        // 4 rows x [p0, p1] = two 128-bit stores, 32 contiguous bytes per thread
+        float4* o = reinterpret_cast<float4*>(P.out + 2 * row0);
+        o[0] = make_float4(po[0], po[1], po[2], po[3]);
+        o[1] = make_float4(po[4], po[5], po[6], po[7]);
     }
     if (nonfinite) fixmask = (1u << R) - 1;     // the float64 path writes NaN for those rows and nothing else touches them
     if (nonfinite) atomicOr(&s_nbad, 1u);
@@ -461,8 +491,9 @@ hfe_synth_kernel(unsigned long long seed, long long row0, long long n, int n_col
 
 // ---- ingest: row-major float64 -> column-major float32 -----------------------------------------------------------------------
 
+template <typename T>
 __global__ void __launch_bounds__(BLOCK_THREADS)
-hfe_ingest_kernel(const double* __restrict__ src, long long n, int nf, float* __restrict__ dst, long long ld,
+hfe_ingest_kernel(const T* __restrict__ src, long long n, int nf, float* __restrict__ dst, long long ld,
                   unsigned int* status) {
     extern __shared__ float s_tile[];     // [BLOCK_THREADS][nf + 1]
     const long long r0 = (long long)blockIdx.x * BLOCK_THREADS;
@@ -470,9 +501,9 @@ hfe_ingest_kernel(const double* __restrict__ src, long long n, int nf, float* __
     const int pitch = nf + 1;
     bool bad = false;
     for (int i = threadIdx.x; i < rows * nf; i += BLOCK_THREADS) {
-        double v = src[r0 * nf + i];
+        T v = src[r0 * nf + i];
         float fv = (float)v;                       // round-to-nearest, like numpy's astype(float32)
-        bad = bad || !(fabs(v) <= 1.7976931348623157e308);
+        bad = bad || !(fabsf(fv) <= 3.402823466e38f);   // NaN/Inf, or a float64 too large for float32
         s_tile[(i / nf) * pitch + (i % nf)] = fv;
     }
     __syncthreads();

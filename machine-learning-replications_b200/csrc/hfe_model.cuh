@@ -33,8 +33,10 @@ namespace hfe {
 constexpr int F = HFE_N_FEATURES;
 constexpr int MAX_MEMBERS = 4;
 constexpr int MAX_SPLITS = 128;       // merged stump table capacity (kernel parameter space)
-constexpr int SV_GROUP = 4;           // support vectors per float4 lane group
-constexpr int SV_ROWS = F + 1;        // float4 rows per group: F weights + folded coefficient
+constexpr int SV_GROUP = 4;           // support vectors per inner tile
+constexpr int SV_STEPS = F + 1;       // table steps per group: F weight steps + one folded-coefficient step
+constexpr int SV_ROWS = 2 * SV_STEPS; // float4 rows per group: each step is (w0,w0,w1,w1),(w2,w2,w3,w3) for FFMA2
+constexpr int SV_PAD_ROWS = 4;        // zero rows after the table so the 2-step-ahead prefetch may over-read
 constexpr int MAX_EDGES = 16;          // coupling-solver discontinuities (6 exist for eps = 0.0025)
 constexpr int SV_CHUNK = 8;           // float32 partial sums are folded into float64 every SV_CHUNK vectors
 
@@ -58,7 +60,7 @@ struct ScoreParams {
     unsigned long long* score;  // [1] or null
     unsigned int* status;       // [HFE_STATUS_WORDS]
     // SVC member
-    const float4* sv_tab;       // [n_groups][SV_ROWS] float4
+    const float4* sv_tab;       // [n_groups][SV_ROWS] float4 (+ SV_PAD_ROWS of zeros)
     const double* sv64;         // [n_sv][F] original order
     const double* dual64;       // [n_sv]
     int n_groups;               // multiple of SV_CHUNK / SV_GROUP
@@ -305,7 +307,7 @@ inline int build_svc(Model* m, const ParsedBlob& pb, uint32_t idx) {
     }
     int padded = ((n_sv + SV_CHUNK - 1) / SV_CHUNK) * SV_CHUNK;
     int n_groups = padded / SV_GROUP;
-    std::vector<float4> tab((size_t)n_groups * SV_ROWS, make_float4(0.f, 0.f, 0.f, 0.f));
+    std::vector<float4> tab((size_t)n_groups * SV_ROWS + SV_PAD_ROWS, make_float4(0.f, 0.f, 0.f, 0.f));
     double max_norm = 0, coef_l2 = 0;
     for (int k = 0; k < n_sv; ++k) {
         int j = order[k];
@@ -314,10 +316,15 @@ inline int build_svc(Model* m, const ParsedBlob& pb, uint32_t idx) {
         for (int d = 0; d < F; ++d) ss += s[d] * s[d];
         max_norm = std::max(max_norm, std::sqrt(ss));
         coef_l2 += coef[j] * coef[j];
+        // step d of a group = two float4: (w0,w0,w1,w1) and (w2,w2,w3,w3); every value is stored twice so that one
+        // 64-bit register pair feeds a packed FFMA2 against a pair of rows
         float* base = reinterpret_cast<float*>(&tab[(size_t)(k / SV_GROUP) * SV_ROWS]);
         int lane = k % SV_GROUP;
-        for (int d = 0; d < F; ++d) base[d * 4 + lane] = (float)(2.0 * P.c_log2 * s[d]);
-        base[F * 4 + lane] = (float)(coef[j] * std::exp2(-P.c_log2 * ss));
+        for (int d = 0; d <= F; ++d) {
+            float v = d < F ? (float)(2.0 * P.c_log2 * s[d]) : (float)(coef[j] * std::exp2(-P.c_log2 * ss));
+            base[d * 8 + lane * 2] = v;
+            base[d * 8 + lane * 2 + 1] = v;
+        }
     }
     // float32 2^x must not overflow: 2c|z||s| <= 100  =>  c|z|^2 <= c*(100/(2c*max|s|))^2
     double zmax = 100.0 / (2.0 * P.c_log2 * std::max(max_norm, 1e-30));

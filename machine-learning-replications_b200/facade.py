@@ -207,6 +207,58 @@ class HFStackB200:
         self.last_status = status
         return status
 
+    def predict_proba_pinned(self, x_host, out_host=None, chunk_rows=1 << 21):
+        """End-to-end host path for large cohorts: ``x_host`` is a row-major float32 (or float64) ``[n, 17]`` torch
+        tensor in pinned host memory; returns a pinned float32 ``[n, 2]`` tensor.  Rows are cut into chunks that
+        alternate between two streams, so the H2D copy of one chunk overlaps the ingest + fused kernel + D2H copy of
+        the other.  Raises ``ValueError`` for NaN/Inf like the numpy entry points.  Synchronises before returning."""
+        import torch
+
+        n = int(x_host.shape[0])
+        if x_host.dim() != 2 or x_host.shape[1] != self.n_features_in_:
+            raise ValueError(f"X has {tuple(x_host.shape)} shape, expected [n, {self.n_features_in_}]")
+        if x_host.dtype not in (torch.float32, torch.float64) or not x_host.is_contiguous():
+            raise ValueError("x_host must be a contiguous float32/float64 tensor")
+        f64 = x_host.dtype == torch.float64
+        if out_host is None:
+            out_host = torch.empty((n, 2), dtype=torch.float32).pin_memory()
+        dev = f"cuda:{self.device}"
+        chunk = int(min(max(chunk_rows, 4), max(n, 4)) + 3) & ~3
+        key = (chunk, x_host.dtype)
+        if getattr(self, "_pipe_key", None) != key:
+            with torch.cuda.device(self.device):
+                self._pipe = [dict(stream=torch.cuda.Stream(device=dev),
+                                   raw=torch.empty((chunk, self.n_features_in_), dtype=x_host.dtype, device=dev),
+                                   col=torch.empty((self.n_features_in_, chunk), dtype=torch.float32, device=dev),
+                                   out=torch.empty((chunk, 2), dtype=torch.float32, device=dev),
+                                   st_in=torch.zeros(capi.STATUS_WORDS, dtype=torch.int32, device=dev),
+                                   st=torch.zeros(capi.STATUS_WORDS, dtype=torch.int32, device=dev),
+                                   flags=torch.zeros(1, dtype=torch.int32, device=dev)) for _ in range(2)]
+            self._pipe_key = key
+        ingest = self._lib.hfe_ingest_rowmajor_f64 if f64 else self._lib.hfe_ingest_rowmajor_f32
+        for slot in self._pipe:
+            slot["flags"].zero_()
+        torch.cuda.current_stream(self.device).synchronize()
+        for i, begin in enumerate(range(0, n, chunk)):
+            rows = min(chunk, n - begin)
+            slot = self._pipe[i & 1]
+            s = slot["stream"]
+            with torch.cuda.stream(s):
+                slot["raw"][:rows].copy_(x_host[begin:begin + rows], non_blocking=True)
+                capi.check(ingest(slot["raw"].data_ptr(), rows, self.n_features_in_, slot["col"].data_ptr(), chunk,
+                                  slot["st_in"].data_ptr(), s.cuda_stream))
+                capi.check(self._lib.hfe_predict_proba(self._handle, slot["col"].data_ptr(), rows, chunk,
+                                                       slot["out"].data_ptr(), slot["st"].data_ptr(), s.cuda_stream))
+                slot["flags"] |= slot["st_in"][:1] | slot["st"][:1]
+                out_host[begin:begin + rows].copy_(slot["out"][:rows], non_blocking=True)
+        bad = 0
+        for slot in self._pipe:
+            slot["stream"].synchronize()
+            bad |= int(slot["flags"].item())
+        if bad & capi.ROW_NONFINITE:
+            raise ValueError("Input X contains NaN or infinity.")
+        return out_host
+
     def predict_proba_f64_device(self, x, n=None, out=None, status=None):
         """Every row through the float64 path (calibration aid)."""
         import torch

@@ -1,0 +1,300 @@
+"""Parity of the CUDA path against the oracle and the committed scikit-learn fixtures, through the C ABI.
+
+Bars (BASELINE.json north_star): leaf indices and hard labels bit-exact; probabilities within 1e-6 absolute.
+"""
+import ctypes as C
+import warnings
+
+import numpy as np
+import pytest
+
+from oracle import stack_oracle as so
+
+pytestmark = pytest.mark.gpu
+PROBA_TOL = 1e-6          # absolute, float32 output vs scikit-learn's float64
+
+
+@pytest.fixture(scope="module")
+def torch_cuda():
+    import torch
+    assert torch.cuda.is_available(), "these tests need a CUDA device"
+    return torch
+
+
+@pytest.fixture(scope="module")
+def clf_for(pkg, cuda_lib, torch_cuda):
+    cache = {}
+
+    def make(case):
+        if case["name"] not in cache:
+            cache[case["name"]] = pkg.HFStackB200(case["blob"], device=0)
+        return cache[case["name"]]
+
+    return make
+
+
+def test_golden_fixture_parity(case, clf_for):
+    clf, g = clf_for(case), case["golden"]
+    X = g["X"].astype(np.float64)
+    proba = clf.predict_proba(X)
+    assert proba.dtype == np.float64 and proba.shape == (X.shape[0], 2)
+    assert np.abs(proba - g["proba"]).max() <= PROBA_TOL
+    assert np.array_equal(proba[:, 0], 1.0 - proba[:, 1])              # p0 is computed from p1, not rounded on its own
+    assert np.array_equal(clf.predict(X), g["label"])                  # hard labels bit-exact, edge rows included
+    assert np.array_equal(clf.apply(X), g["leaves"].astype(np.int64))  # leaf indices bit-exact
+    assert np.abs(clf.transform(X) - g["meta"]).max() <= 2e-6
+    assert np.abs(clf.decision_function(X) - so.decision_function(case["arrays"], X)).max() <= 5e-6
+    assert np.array_equal(clf.classes_, [0.0, 1.0]) and clf.n_features_in_ == 17
+
+
+def test_predict_hf_default_patient(published, clf_for, pkg):
+    # what predict_hf.py:29-40 does, with the facade in place of the unpickled model
+    params = dict(zip(pkg.synth.SCHEMA_NAMES, [1, 1, 0, 0, 1, 0, 1, 1, 0, 0, 0, 0, 0, 13, 0, 0, 55]))
+    score = clf_for(published).predict_proba(pkg.patient_vector(params))
+    assert abs(score[0, 1] - 0.27090030089940764) <= PROBA_TOL
+    assert "{0:.2f}".format(100 * score[0, 1]) == "27.09"
+
+
+@pytest.mark.parametrize("n", [1, 2, 3, 4, 5, 31, 32, 33, 127, 1023, 1024, 1025, 4099])
+def test_ragged_row_counts(published, clf_for, pkg, n):
+    X = pkg.synth.host_rows(published["specs"], 11, 777, n).astype(np.float64)
+    got = clf_for(published).predict_proba(X)
+    assert np.abs(got - so.predict_proba(published["arrays"], X)).max() <= PROBA_TOL
+    assert np.array_equal(clf_for(published).predict(X), so.predict(published["arrays"], X))
+
+
+def test_input_layouts_and_dtypes(published, clf_for, pkg):
+    clf = clf_for(published)
+    X = pkg.synth.host_rows(published["specs"], 3, 0, 200)
+    base = clf.predict_proba(X.astype(np.float64))
+    assert np.array_equal(clf.predict_proba(X), base)                                  # float32
+    assert np.array_equal(clf.predict_proba(np.asfortranarray(X.astype(np.float64))), base)
+    assert np.array_equal(clf.predict_proba(X.astype(np.int64)), base)                 # predict_hf.py passes ints
+    assert np.array_equal(clf.predict_proba(X.tolist()), base)
+
+
+def test_error_behaviour(published, clf_for):
+    clf = clf_for(published)
+    with pytest.raises(ValueError):
+        clf.predict_proba(np.zeros(17))
+    with pytest.raises(ValueError):
+        clf.predict_proba(np.zeros((3, 16)))
+    with pytest.raises(ValueError):
+        clf.predict_proba(np.zeros((0, 17)))
+    bad = np.zeros((5, 17))
+    bad[2, 4] = np.nan
+    with pytest.raises(ValueError):
+        clf.predict_proba(bad)
+    big = np.zeros((5, 17))
+    big[0, 0] = 1e300                           # finite in float64, infinite once cast to float32 (GBC cast)
+    with pytest.raises(ValueError):
+        clf.predict_proba(big)
+
+
+def test_device_status_flags_nonfinite(published, clf_for, torch_cuda):
+    torch = torch_cuda
+    clf = clf_for(published)
+    x = torch.zeros((17, 64), dtype=torch.float32, device="cuda")
+    x[6] = 1.0
+    x[3, 10] = float("inf")
+    st = clf.new_status()
+    out = clf.predict_proba_device(x, n=64, status=st)
+    torch.cuda.synchronize()
+    assert int(st[0].item()) & 1
+    assert torch.isnan(out[10]).all() and torch.isfinite(out[11]).all()
+
+
+def test_misaligned_or_short_matrix_is_refused(published, clf_for, pkg, torch_cuda):
+    torch = torch_cuda
+    clf = clf_for(published)
+    lib = pkg.capi.load_library()
+    x = torch.zeros((17, 66), dtype=torch.float32, device="cuda")
+    out = torch.zeros((64, 2), dtype=torch.float32, device="cuda")
+    st = clf.new_status()
+    rc = lib.hfe_predict_proba(clf._handle, x.data_ptr(), 64, 66, out.data_ptr(), st.data_ptr(), None)
+    assert rc == 1 and b"aligned" in lib.hfe_last_error_string()
+    rc = lib.hfe_predict_proba(clf._handle, x.data_ptr(), 64, 32, out.data_ptr(), st.data_ptr(), None)
+    assert rc == 1
+    rc = lib.hfe_predict_proba(clf._handle, x.data_ptr(), 0, 64, out.data_ptr(), st.data_ptr(), None)
+    assert rc == 0                                                  # empty batch is a no-op at the C level
+
+
+def test_synth_rows_bit_identical_host_device(case, pkg, torch_cuda):
+    x = pkg.synth_rows_device(case["specs"], 2020, 999_999_000, 5000)
+    host = pkg.synth.host_rows(case["specs"], 2020, 999_999_000, 5000)
+    assert np.array_equal(x[:, :5000].T.cpu().numpy(), host)
+
+
+def test_large_batch_properties(case, clf_for, pkg, torch_cuda):
+    """10 M rows (BASELINE config 2): size-independent properties + oracle on a strided sample."""
+    torch = torch_cuda
+    clf = clf_for(case)
+    n = 10_000_000
+    x = pkg.synth_rows_device(case["specs"], 2020, 0, n)
+    st = clf.new_status()
+    out = clf.predict_proba_device(x, n=n, status=st)
+    torch.cuda.synchronize()
+    assert int(st[0].item()) == 0
+    assert int(st[1].item()) < n // 2000                               # float64 re-evaluations stay rare
+    assert bool(((out[:, 0] + out[:, 1]) - 1.0).abs().max() <= 1.2e-7)
+    assert bool((out >= 0).all()) and bool((out <= 1).all())
+    # shard invariance: scoring two halves separately is byte-identical to scoring the whole
+    half = n // 2
+    a = clf.predict_proba_device(x[:, :half], n=half)
+    b = clf.predict_proba_device(x[:, half:], n=n - half)
+    torch.cuda.synchronize()
+    assert torch.equal(torch.cat([a, b]), out)
+    # the float32 fast path agrees with the all-float64 path on every row of a 2 M slice
+    m = 2_000_000
+    o64 = clf.predict_proba_f64_device(x, n=m)
+    torch.cuda.synchronize()
+    assert float((out[:m].double() - o64).abs().max().item()) <= 5e-7
+    # oracle on a strided sample spread over the whole batch
+    idx = np.arange(0, n, n // 20000)[:20000]
+    Xs = x[:, torch.from_numpy(idx).cuda()].T.cpu().numpy().astype(np.float64)
+    want = so.predict_proba(case["arrays"], Xs)
+    got = out[torch.from_numpy(idx).cuda()].cpu().numpy().astype(np.float64)
+    assert np.abs(got - want).max() <= PROBA_TOL
+    lab = torch.empty(n, dtype=torch.uint8, device="cuda")
+    clf.score_device(x, n=n, labels=lab)
+    torch.cuda.synchronize()
+    assert np.array_equal(lab[torch.from_numpy(idx).cuda()].cpu().numpy(),
+                          (so.decision_function(case["arrays"], Xs) > 0).astype(np.uint8))
+
+
+def test_solver_edge_rows_take_the_float64_path(published, clf_for, pkg, torch_cuda):
+    """Rows engineered to sit on the coupling solver's plateau edge must still match scikit-learn exactly in branch."""
+    g = published["golden"]
+    X = g["X"][int(g["n_appendix"]) + 1024:].astype(np.float64)        # the edge rows make_golden picked
+    clf = clf_for(published)
+    got = clf.predict_proba(X)
+    want = g["proba"][int(g["n_appendix"]) + 1024:]
+    assert np.abs(got - want).max() <= PROBA_TOL
+
+
+def test_pinned_host_pipeline(case, clf_for, pkg, torch_cuda):
+    torch = torch_cuda
+    clf = clf_for(case)
+    n = 300_001
+    X = pkg.synth.host_rows(case["specs"], 9, 0, n)
+    xh = torch.from_numpy(X).pin_memory()
+    got = clf.predict_proba_pinned(xh, chunk_rows=1 << 16).numpy()
+    x = clf.to_device_colmajor(X)
+    ref = clf.predict_proba_device(x, n=n).cpu().numpy()
+    assert np.array_equal(got, ref)
+    got64 = clf.predict_proba_pinned(torch.from_numpy(X.astype(np.float64)).pin_memory(), chunk_rows=1 << 17).numpy()
+    assert np.array_equal(got64, ref)
+    bad = X.copy()
+    bad[123456, 5] = np.nan
+    with pytest.raises(ValueError):
+        clf.predict_proba_pinned(torch.from_numpy(bad).pin_memory())
+
+
+def test_permuted_column_pass_and_score_count(published, clf_for, pkg, torch_cuda):
+    """One permutation-importance pass: column read through an index array == scoring the materialised shuffle."""
+    torch = torch_cuda
+    clf = clf_for(published)
+    n = 100_003
+    X = pkg.synth.host_rows(published["specs"], 4, 0, n)
+    rng = np.random.RandomState(0)
+    perm = rng.permutation(n).astype(np.int32)
+    col = 13
+    Xp = X.copy()
+    Xp[:, col] = X[perm, col]
+    x = clf.to_device_colmajor(X)
+    xp = clf.to_device_colmajor(Xp)
+    y = (so.decision_function(published["arrays"], X.astype(np.float64)) > 0).astype(np.uint8)
+    y_dev = torch.from_numpy(y).cuda()
+    out_a = torch.empty((n, 2), dtype=torch.float32, device="cuda")
+    out_b = torch.empty_like(out_a)
+    lab = torch.empty(n, dtype=torch.uint8, device="cuda")
+    score = torch.zeros(1, dtype=torch.int64, device="cuda")
+    clf.score_device(x, n=n, perm_col=col, perm_idx=torch.from_numpy(perm).cuda(), out=out_a, labels=lab, y=y_dev,
+                     score=score)
+    clf.score_device(xp, n=n, out=out_b)
+    torch.cuda.synchronize()
+    assert torch.equal(out_a, out_b)
+    assert int(score.item()) == int((lab.cpu().numpy() == y).sum())
+    base = torch.zeros(1, dtype=torch.int64, device="cuda")
+    clf.score_device(x, n=n, y=y_dev, score=base)
+    torch.cuda.synchronize()
+    assert int(base.item()) == n                                         # unpermuted labels reproduce y exactly
+
+
+def test_model_info_and_members(case, clf_for):
+    info = clf_for(case).info
+    assert info.n_features == 17 and info.n_members == 3
+    assert list(info.member_kind)[:3] == [1, 2, 3]
+    assert info.n_trees == 100 and info.tree_mode == 1 and 1 <= info.n_merged_splits <= 100
+    assert info.n_support_vectors == case["arrays"].members[0].sv.shape[0]
+
+
+def test_general_tree_models(pkg, clf_for, published, torch_cuda):
+    """Depth>1 boosted trees (general node tables) with and without the SVC member, against the oracle."""
+    import copy
+    rng = np.random.default_rng(5)
+    ex = pkg.export
+
+    def random_tree(depth, leaves_target):
+        left, right, feat, thr, val = [-1], [-1], [-2], [-2.0], [rng.normal() * 0.3]
+        frontier = [(0, 0)]
+        n_leaves = 1
+        while frontier and n_leaves < leaves_target:
+            i, d = frontier.pop(rng.integers(len(frontier)))
+            if d >= depth:
+                continue
+            f = int(rng.integers(17))
+            t = {13: rng.integers(10, 30) + 0.5, 16: rng.integers(45, 75) + 0.25, 15: rng.integers(0, 4) + 0.5,
+                 6: 1.5}.get(f, 0.5)
+            left[i], right[i], feat[i], thr[i] = len(left), len(left) + 1, f, float(t)
+            for _ in range(2):
+                left.append(-1); right.append(-1); feat.append(-2); thr.append(-2.0); val.append(rng.normal() * 0.3)
+            frontier += [(left[i], d + 1), (right[i], d + 1)]
+            n_leaves += 1
+        return ex.TreeTable(left=np.array(left, np.int32), right=np.array(right, np.int32),
+                            feature=np.array(feat, np.int32), threshold=np.array(thr), value=np.array(val))
+
+    base = published["arrays"]
+    gbt = ex.GbtMember(name="gbc", init_raw=-1.2, learning_rate=0.05,
+                       trees=[random_tree(8, 40) for _ in range(60)])
+    with_svc = copy.deepcopy(base)
+    with_svc.members[1] = gbt
+    no_svc = ex.ModelArrays(n_features=17, members=[gbt, base.members[2]], final_coef=np.array([1.3, 2.1]),
+                            final_intercept=-1.1, classes=base.classes)
+    X = pkg.synth.host_rows(published["specs"], 21, 0, 20_000).astype(np.float64)
+    for arrays in (with_svc, no_svc):
+        clf = pkg.HFStackB200.from_arrays(arrays)
+        assert clf.info.tree_mode == 2
+        assert np.abs(clf.predict_proba(X) - so.predict_proba(arrays, X)).max() <= PROBA_TOL
+        assert np.array_equal(clf.predict(X), so.predict(arrays, X))
+        g = next(m for m in arrays.members if m.kind == "gbt")
+        assert np.array_equal(clf.apply(X[:3000]), so.gbt_apply(g, X[:3000]))
+        clf.close()
+
+
+def test_live_sklearn_object_drop_in(pkg, torch_cuda):
+    """train_ensemble_public.py:61-63 with the facade swapped in for clf after fit."""
+    from sklearn.ensemble import GradientBoostingClassifier, StackingClassifier
+    from sklearn.linear_model import LogisticRegression
+    from sklearn.pipeline import make_pipeline
+    from sklearn.preprocessing import StandardScaler
+    from sklearn.svm import SVC
+
+    specs = pkg.synth.schema_specs()
+    X = pkg.synth.host_rows(specs, 5, 0, 500).astype(np.float64)
+    y = ((X[:, 3] + X[:, 0] + (X[:, 13] > 20)) >= 2).astype(float)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        clf = StackingClassifier(
+            estimators=[("svc", make_pipeline(StandardScaler(), SVC(class_weight="balanced", probability=True,
+                                                                    random_state=2020))),
+                        ("gbc", GradientBoostingClassifier(n_estimators=100, max_depth=1, random_state=2020)),
+                        ("lg", LogisticRegression(class_weight="balanced", penalty="l1", solver="liblinear"))],
+            final_estimator=LogisticRegression(class_weight="balanced")).fit(X, y)
+        Xs = pkg.synth.host_rows(specs, 6, 10_000, 5000).astype(np.float64)
+        fast = pkg.HFStackB200.from_sklearn(clf)
+        y_pred = fast.predict_proba(Xs)
+        assert np.abs(y_pred - clf.predict_proba(Xs)).max() <= PROBA_TOL
+        assert np.array_equal(fast.predict(Xs), clf.predict(Xs))
+        gi = 1
+        assert np.array_equal(fast.apply(Xs), clf.estimators_[gi].apply(Xs)[:, :, 0].astype(np.int64))
