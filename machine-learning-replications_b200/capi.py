@@ -6,7 +6,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libhfe.so")
+LIB_PATH = os.environ.get("HFE_LIB") or os.path.join(_HERE, "libhfe.so")   # HFE_LIB: development override
 
 HFE_OK = 0
 HFE_ERR_NONFINITE_INPUT = 5

@@ -30,8 +30,8 @@ int launch_score(const Model* m, const ScoreParams& P, cudaStream_t stream) {
     size_t sv_bytes = 0;
     int smem_groups = 0;
     if (SVC) {
-        smem_groups = std::min(P.n_groups, TM == 2 ? 64 : MAX_SMEM_GROUPS);
-        sv_bytes = ((size_t)smem_groups * SV_ROWS + SV_PAD_ROWS) * sizeof(float4);
+        smem_groups = std::min(P.n_groups, TM == 2 ? 128 : MAX_SMEM_GROUPS);
+        sv_bytes = ((size_t)smem_groups * SV_STEPS + SV_PAD_ROWS) * sizeof(float4);
     }
     size_t smem = sv_bytes + (TM == 2 ? (size_t)F * BLOCK_ROWS * sizeof(float) : 0);
     auto kernel = hfe_score_kernel<SVC, TM>;
@@ -39,7 +39,7 @@ int launch_score(const Model* m, const ScoreParams& P, cudaStream_t stream) {
     static cudaError_t attr_err[16];
     int dev = m->device & 15;
     std::call_once(once[dev], [&] {
-        attr_err[dev] = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024);
+        attr_err[dev] = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024);
     });
     if (attr_err[dev] != cudaSuccess)
         return fail(HFE_ERR_CUDA, std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(attr_err[dev]));

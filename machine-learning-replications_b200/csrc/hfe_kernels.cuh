@@ -18,13 +18,16 @@
 
 namespace hfe {
 
-constexpr int BLOCK_THREADS = 256;
+#ifndef HFE_BLOCK_THREADS
+#define HFE_BLOCK_THREADS 256
+#endif
+constexpr int BLOCK_THREADS = HFE_BLOCK_THREADS;
 constexpr int ROWS_PER_THREAD = 4;
 constexpr int BLOCK_ROWS = BLOCK_THREADS * ROWS_PER_THREAD;
-constexpr int MAX_SMEM_GROUPS = 160;      // support-vector groups staged per pass (160*36*16 B = 90 KB)
+constexpr int MAX_SMEM_GROUPS = 384;      // support-vector groups staged per pass (384*18*16 B = 108 KB; 2 blocks/SM)
 constexpr int TREE_CHUNK = 16;            // float32 partial sums over trees are folded into float64 every 16 trees
 #ifndef HFE_MIN_BLOCKS
-#define HFE_MIN_BLOCKS 2                  // resident blocks per SM the fused kernel is compiled for (register cap)
+#define HFE_MIN_BLOCKS 2                  // resident blocks per SM the fused kernel is compiled for (128-register cap)
 #endif
 
 __device__ __forceinline__ float ex2_approx(float x) {
@@ -37,6 +40,134 @@ __device__ __noinline__ double expit_f64(double x) {
     // scipy.special.expit (what SK/_loss/link.py:180 and SK/linear_model/_base.py:429-451 call), sign-split
     double e = exp(-fabs(x));
     return x >= 0 ? 1.0 / (1.0 + e) : e / (1.0 + e);
+}
+
+// ---- fast float64 helpers for the per-row epilogue of the fused kernel -----------------------------------------------
+// The epilogue runs once per row but in float64, so the library exp() / division (special-case branches, ~30-40
+// instructions each) would cost as much as a third of the whole pass.  These versions are branch-free, accurate to
+// ~1e-15 relative on the ranges they are given, and are only used where a guard band protects every branch that
+// depends on them; the cooperative float64 re-evaluation path keeps the library versions.
+__device__ __forceinline__ double rcp_fast(double x) {          // x in [1e-16, 1e16], normal
+    double y;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));       // MUFU.RCP64H, ~2^-23 relative
+    double e = fma(-x, y, 1.0);
+    y = fma(y, e, y);
+    e = fma(-x, y, 1.0);
+    return fma(y, e, y);
+}
+
+__device__ __forceinline__ double exp_neg_fast(double x) {      // exp(x) for x <= 0
+    x = fmax(x, -700.0);
+    const double shifter = 6755399441055744.0;                  // 1.5 * 2^52: rint() by addition
+    double t = fma(x, 1.4426950408889634074, shifter);
+    int k = __double2loint(t);
+    double kd = t - shifter;
+    double r = fma(kd, -6.93147180369123816490e-01, x);
+    r = fma(kd, -1.90821492927058770002e-10, r);                // |r| <= ln2/2
+    double p = 2.50521083854417187751e-08;                      // 1/11!
+    p = fma(p, r, 2.75573192239858906526e-07);
+    p = fma(p, r, 2.75573192239858906526e-06);
+    p = fma(p, r, 2.48015873015873015873e-05);
+    p = fma(p, r, 1.98412698412698412698e-04);
+    p = fma(p, r, 1.38888888888888888889e-03);
+    p = fma(p, r, 8.33333333333333333333e-03);
+    p = fma(p, r, 4.16666666666666666667e-02);
+    p = fma(p, r, 1.66666666666666666667e-01);
+    p = fma(p, r, 0.5);
+    p = fma(p, r, 1.0);
+    p = fma(p, r, 1.0);
+    return __hiloint2double(__double2hiint(p) + (k << 20), __double2loint(p));   // p * 2^k, k >= -1010
+}
+
+// Platt + clamp + coupling + links + combiner for R rows at once, the R dependency chains interleaved.
+template <int R>
+__device__ __forceinline__ void finish_rows_fast(const ScoreParams& P, bool has_svc, bool has_gbt, bool has_lin,
+                                                 const double (&f_svc)[R], const double (&raw)[R],
+                                                 const double (&zl)[R], double (&p1)[R], double (&zfin)[R],
+                                                 double (&member)[3][R], bool (&uncertain)[R]) {
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        uncertain[r] = false;
+        member[0][r] = member[1][r] = member[2][r] = 0.0;
+    }
+    if (has_svc) {
+        double q00[R], q11[R], q01[R], iq00[R], iq11[R], a0[R], a1[R];
+        bool done[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            double t = fma(f_svc[r], P.prob_a, P.prob_b);
+            double e = exp_neg_fast(-fabs(t));
+            double inv = rcp_fast(1.0 + e);
+            double r01 = t >= 0 ? e * inv : inv;                      // svm.cpp:2035-2043
+            r01 = fmin(fmax(r01, 1e-7), 1.0 - 1e-7);                  // svm.cpp:2932-2941
+            double r10 = 1.0 - r01;
+            q00[r] = r10 * r10; q11[r] = r01 * r01; q01[r] = -r10 * r01;
+            iq00[r] = rcp_fast(q00[r]); iq11[r] = rcp_fast(q11[r]);
+            a0[r] = 0.5; a1[r] = 0.5;
+            done[r] = !(t == t);                                      // NaN rows skip the solver
+            double nearest = 1e300;
+            for (int k = 0; k < P.n_edges; ++k) nearest = fmin(nearest, fabs(t - P.edges[k]));
+            uncertain[r] = !(nearest >= P.solver_guard);
+        }
+#pragma unroll 1
+        for (int iter = 0; iter < 100; ++iter) {                      // svm.cpp:2046-2107, k = 2
+            bool all_done = true;
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                if (done[r]) continue;
+                double qp0 = q00[r] * a0[r] + q01[r] * a1[r];
+                double qp1 = q01[r] * a0[r] + q11[r] * a1[r];
+                double pqp = a0[r] * qp0 + a1[r] * qp1;
+                double err = fmax(fabs(qp0 - pqp), fabs(qp1 - pqp));
+                if (err < 0.005 / 2) { done[r] = true; continue; }
+                all_done = false;
+                double diff = (pqp - qp0) * iq00[r];
+                double inv = rcp_fast(1.0 + diff);
+                a0[r] = (a0[r] + diff) * inv;
+                a1[r] = a1[r] * inv;
+                pqp = (pqp + diff * (diff * q00[r] + 2.0 * qp0)) * inv * inv;
+                qp1 = (qp1 + diff * q01[r]) * inv;
+                diff = (pqp - qp1) * iq11[r];
+                inv = rcp_fast(1.0 + diff);
+                a1[r] = (a1[r] + diff) * inv;
+                a0[r] = a0[r] * inv;
+            }
+            if (all_done) break;
+        }
+#pragma unroll
+        for (int r = 0; r < R; ++r) member[0][r] = a1[r];
+    }
+    if (has_gbt) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            double e = exp_neg_fast(-fabs(raw[r]));
+            double inv = rcp_fast(1.0 + e);
+            member[1][r] = raw[r] >= 0 ? inv : e * inv;
+        }
+    }
+    if (has_lin) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            double e = exp_neg_fast(-fabs(zl[r]));
+            double inv = rcp_fast(1.0 + e);
+            member[2][r] = zl[r] >= 0 ? inv : e * inv;
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        double z = P.final_intercept;
+#pragma unroll
+        for (int slot = 0; slot < MAX_MEMBERS; ++slot) {              // estimators_ order
+            if (has_svc && slot == P.slot_svc) z = fma(P.final_coef[slot], member[0][r], z);
+            else if (has_gbt && slot == P.slot_gbt) z = fma(P.final_coef[slot], member[1][r], z);
+            else if (has_lin && slot == P.slot_lin) z = fma(P.final_coef[slot], member[2][r], z);
+        }
+        double e = exp_neg_fast(-fabs(z));
+        double inv = rcp_fast(1.0 + e);
+        zfin[r] = z;
+        p1[r] = z >= 0 ? inv : e * inv;
+        uncertain[r] = uncertain[r] || !(fabs(z) >= P.label_guard);
+    }
 }
 
 struct RowResult {
@@ -196,8 +327,9 @@ template <bool SVC, int TREE_MODE>
 __global__ void __launch_bounds__(BLOCK_THREADS, HFE_MIN_BLOCKS)
 hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    float4* s_sv = reinterpret_cast<float4*>(smem_raw);                       // [smem_groups][SV_ROWS]
-    float* s_xt = reinterpret_cast<float*>(smem_raw) + (SVC ? ((size_t)smem_groups * SV_ROWS + SV_PAD_ROWS) * 4 : 0);  // [F][BLOCK_ROWS]
+    float4* s_sv = reinterpret_cast<float4*>(smem_raw);                       // [smem_groups][SV_STEPS] (+pad)
+    float* s_xt = reinterpret_cast<float*>(smem_raw) +
+                  (SVC ? ((size_t)smem_groups * SV_STEPS + SV_PAD_ROWS) * 4 : 0);             // [F][BLOCK_ROWS]
     __shared__ double s_x[F], s_z[F], s_red[2 * BLOCK_THREADS / 32];
     __shared__ unsigned int s_nfix, s_nbad, s_hits;
     __shared__ unsigned short s_fix[BLOCK_ROWS];
@@ -221,11 +353,12 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
             for (int r = 0; r < R; ++r) xv[f][r] = (row0 + r < P.n) ? load_feature(P, f, row0 + r) : 0.0f;
         }
     }
-    bool nonfinite = false;
+    float finite_probe = 0.f;                       // x * 0 is NaN exactly when x is NaN or +-Inf
 #pragma unroll
     for (int f = 0; f < F; ++f)
 #pragma unroll
-        for (int r = 0; r < R; ++r) nonfinite = nonfinite || !(fabsf(xv[f][r]) <= 3.402823466e38f);
+        for (int r = 0; r < R; ++r) finite_probe = fmaf(xv[f][r], 0.f, finite_probe);
+    const bool nonfinite = !(finite_probe == 0.f);
 
     if (TREE_MODE == 2) {
 #pragma unroll
@@ -283,132 +416,168 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
         }
     }
 
-    // ---- logistic member + standardisation (float64), z rounded once to float32 for the RBF sum -----------------------
+    // ---- logistic member (float64) and standardisation (float32, mean split hi+lo so x - mean stays exact-ish) -------
     // z2[f][p] packs rows (2p, 2p+1) of feature f into one 64-bit register pair for FFMA2.
-    double zl[R], zz[R];
+    double zl[R];
+    float zz32[R];
 #pragma unroll
-    for (int r = 0; r < R; ++r) { zl[r] = P.lin_intercept; zz[r] = 0.0; }
+    for (int r = 0; r < R; ++r) { zl[r] = P.lin_intercept; zz32[r] = 0.f; }
     float2 z2[F][R / 2];
 #pragma unroll
     for (int f = 0; f < F; ++f) {
         float zf[R];
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            double xd = (double)xv[f][r];
-            if (has_lin) zl[r] = fma(xd, P.lin_coef[f], zl[r]);
+            if (has_lin) zl[r] = fma((double)xv[f][r], P.lin_coef[f], zl[r]);
             zf[r] = 0.f;
             if (SVC) {
-                double zd = (xd - P.mean[f]) * P.inv_scale[f];
-                zz[r] = fma(zd, zd, zz[r]);
-                zf[r] = (float)zd;
+                zf[r] = ((xv[f][r] - P.mean_hi[f]) - P.mean_lo[f]) * P.inv_scale32[f];
+                zz32[r] = fmaf(zf[r], zf[r], zz32[r]);
             }
         }
 #pragma unroll
         for (int p = 0; p < R / 2; ++p) z2[f][p] = make_float2(zf[2 * p], zf[2 * p + 1]);
     }
 
-    // ---- RBF sum: 4 support vectors x 4 rows per tile, packed FFMA2, table streamed from shared memory ------------------
-    // The table is a linear stream of steps (two float4 each); a 3-deep register ring keeps the LDS.128 two steps
-    // ahead of their first use.
+    // ---- RBF sum: 4 support vectors x 4 rows per tile, packed FFMA2 ------------------------------------------------------
+    // Each table step is one float4 = the weights of 4 support vectors for one feature (step F: their folded
+    // coefficients).  A weight enters FFMA2 as a broadcast scalar operand (SASS ``Rw.F32``); the two 64-bit operands
+    // are a pair of rows of z and the pair's running exponents.  The table streams from shared memory through a
+    // 3-deep register ring (LDS.128 issued two steps ahead of first use).  The 16 exp2 (MUFU) + 8 coefficient FFMA2s
+    // of group g-1 are interleaved with the FFMA2s of group g so every warp uses the XU and FMA pipes evenly instead
+    // of in bursts (warps of a block run in lockstep).
     double acc64[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) acc64[r] = 0.0;
     if (SVC) {
         for (int g0 = 0; g0 < P.n_groups; g0 += smem_groups) {
-            int ng = min(smem_groups, P.n_groups - g0);
+            const int ng = min(smem_groups, P.n_groups - g0);
             __syncthreads();
-            for (int i = tid; i < ng * SV_ROWS + SV_PAD_ROWS; i += BLOCK_THREADS)
-                s_sv[i] = (i < ng * SV_ROWS) ? __ldg(P.sv_tab + (size_t)g0 * SV_ROWS + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int i = tid; i < ng * SV_STEPS + SV_PAD_ROWS; i += BLOCK_THREADS)
+                s_sv[i] = (i < ng * SV_STEPS) ? __ldg(P.sv_tab + (size_t)g0 * SV_STEPS + i)
+                                              : make_float4(0.f, 0.f, 0.f, 0.f);
             __syncthreads();
             const float4* tab = s_sv;
-            float4 ring_a[3], ring_b[3];
-            ring_a[0] = tab[0]; ring_b[0] = tab[1];
-            ring_a[1] = tab[2]; ring_b[1] = tab[3];
+            float4 ring[3];
+            ring[0] = tab[0]; ring[1] = tab[1];
+            float2 tprev[SV_GROUP][R / 2], acc2[R / 2];
+            float cprev[SV_GROUP];
+#pragma unroll
+            for (int q = 0; q < SV_GROUP; ++q) {
+                cprev[q] = 0.f;
+#pragma unroll
+                for (int p = 0; p < R / 2; ++p) tprev[q][p] = make_float2(-1000.f, -1000.f);   // exp2 -> 0
+            }
+#pragma unroll
+            for (int p = 0; p < R / 2; ++p) acc2[p] = make_float2(0.f, 0.f);
+
+            // exp2 + coefficient accumulate for element k (0..7) of the previous group: (q, p) = (k / 2, k % 2)
+            auto exp_acc = [&](int k) {
+                const int q = k >> 1, p = k & 1;
+                float2 e = make_float2(ex2_approx(tprev[q][p].x), ex2_approx(tprev[q][p].y));
+                acc2[p] = __ffma2_rn(e, make_float2(cprev[q], cprev[q]), acc2[p]);
+            };
+
 #pragma unroll 1
-            for (int g = 0; g < ng; g += SV_CHUNK / SV_GROUP) {
-                float2 acc2[R / 2];
+            for (int g = 0; g < ng; ++g) {
+                float2 t2[SV_GROUP][R / 2];
 #pragma unroll
-                for (int p = 0; p < R / 2; ++p) acc2[p] = make_float2(0.f, 0.f);
+                for (int st = 0; st < SV_STEPS; ++st) {
+                    ring[(st + 2) % 3] = tab[st + 2];         // SV_STEPS % 3 == 0: same ring slot in every group
+                    const float4 w4 = ring[st % 3];
+                    const float w[SV_GROUP] = {w4.x, w4.y, w4.z, w4.w};
+                    if (st == 0) {
 #pragma unroll
-                for (int h = 0; h < SV_CHUNK / SV_GROUP; ++h) {
-                    float2 t2[SV_GROUP][R / 2];
-#pragma unroll
-                    for (int st = 0; st < SV_STEPS; ++st) {
-                        // SV_STEPS % 3 == 0, so the ring slot of a step is the same in every group
-                        ring_a[(st + 2) % 3] = tab[2 * (st + 2)];
-                        ring_b[(st + 2) % 3] = tab[2 * (st + 2) + 1];
-                        const float4 a = ring_a[st % 3], b = ring_b[st % 3];
-                        const float2 w[SV_GROUP] = {make_float2(a.x, a.y), make_float2(a.z, a.w),
-                                                    make_float2(b.x, b.y), make_float2(b.z, b.w)};
-                        if (st == 0) {
+                        for (int p = 0; p < R / 2; ++p)
 #pragma unroll
                             for (int q = 0; q < SV_GROUP; ++q)
+                                t2[q][p] = __fmul2_rn(z2[0][p], make_float2(w[q], w[q]));
+                    } else if (st < F) {
 #pragma unroll
-                                for (int p = 0; p < R / 2; ++p) t2[q][p] = __fmul2_rn(z2[0][p], w[q]);
-                        } else if (st < F) {
-#pragma unroll
-                            for (int q = 0; q < SV_GROUP; ++q)
-#pragma unroll
-                                for (int p = 0; p < R / 2; ++p) t2[q][p] = __ffma2_rn(z2[st][p], w[q], t2[q][p]);
-                        } else {
+                        for (int p = 0; p < R / 2; ++p)
 #pragma unroll
                             for (int q = 0; q < SV_GROUP; ++q)
+                                t2[q][p] = __ffma2_rn(z2[st][p], make_float2(w[q], w[q]), t2[q][p]);
+                    }
+                    // previous group's exponentials, spread over steps 1,3,...,15
+                    if ((st & 1) && st < 2 * SV_GROUP * (R / 2)) exp_acc(st >> 1);
+                    if (st == F) {
 #pragma unroll
-                                for (int p = 0; p < R / 2; ++p) {
-                                    float2 e = make_float2(ex2_approx(t2[q][p].x), ex2_approx(t2[q][p].y));
-                                    acc2[p] = __ffma2_rn(w[q], e, acc2[p]);
-                                }
+                        for (int q = 0; q < SV_GROUP; ++q) {
+                            cprev[q] = w[q];
+#pragma unroll
+                            for (int p = 0; p < R / 2; ++p) tprev[q][p] = t2[q][p];
                         }
                     }
-                    tab += SV_ROWS;
                 }
+                tab += SV_STEPS;
+                // fold the float32 partial sums (4 vectors) into float64
 #pragma unroll
                 for (int p = 0; p < R / 2; ++p) {
                     acc64[2 * p] += (double)acc2[p].x;
                     acc64[2 * p + 1] += (double)acc2[p].y;
+                    acc2[p] = make_float2(0.f, 0.f);
                 }
+            }
+            // drain: the last group's exponentials
+#pragma unroll
+            for (int k = 0; k < SV_GROUP * (R / 2); ++k) exp_acc(k);
+#pragma unroll
+            for (int p = 0; p < R / 2; ++p) {
+                acc64[2 * p] += (double)acc2[p].x;
+                acc64[2 * p + 1] += (double)acc2[p].y;
             }
         }
     }
 
-    // ---- float64 epilogue: Platt, coupling, links, combiner -------------------------------------------------------------
+    // ---- float64 epilogue: Platt, coupling, links, combiner (4 rows interleaved) ------------------------------------------
+    double f_svc[R], p1[R], zfin[R], member[3][R];
+    bool unc[R];
     unsigned fixmask = 0;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        f_svc[r] = 0.0;
+        if (SVC) {
+            double gzz = P.gamma * (double)zz32[r];                     // gamma |z|^2
+            f_svc[r] = fma(acc64[r], exp_neg_fast(-gzz), P.svc_intercept);
+            if (!(gzz <= P.zz_limit)) fixmask |= 1u << r;               // float32 2^x range guard (or NaN)
+        }
+    }
+    finish_rows_fast<R>(P, SVC, TREE_MODE != 0, has_lin, f_svc, raw, zl, p1, zfin, member, unc);
     unsigned char lab[R];
     float po[2 * R];
 #pragma unroll
     for (int r = 0; r < R; ++r) {
-        lab[r] = 0;
-        po[2 * r] = po[2 * r + 1] = 0.f;
+        po[2 * r] = (float)(1.0 - p1[r]);
+        po[2 * r + 1] = (float)p1[r];
+        lab[r] = zfin[r] > 0 ? 1 : 0;
+        if (unc[r]) fixmask |= 1u << r;
         if (row0 + r >= P.n) continue;
-        double f_svc = 0.0;
-        bool uncertain = false;
-        if (SVC) {
-            double czz = P.c_log2 * zz[r];
-            f_svc = acc64[r] * exp2(-czz) + P.svc_intercept;
-            uncertain = !(czz <= P.zz_limit);
+        if (P.out && !full) { P.out[2 * (row0 + r)] = po[2 * r]; P.out[2 * (row0 + r) + 1] = po[2 * r + 1]; }
+        if (P.out64) { P.out64[2 * (row0 + r)] = 1.0 - p1[r]; P.out64[2 * (row0 + r) + 1] = p1[r]; }
+        if (P.labels) P.labels[row0 + r] = lab[r];
+        if (P.decision) P.decision[row0 + r] = zfin[r];
+        if (P.meta) {
+            if (P.slot_svc >= 0) P.meta[(row0 + r) * P.n_members + P.slot_svc] = member[0][r];
+            if (P.slot_gbt >= 0) P.meta[(row0 + r) * P.n_members + P.slot_gbt] = member[1][r];
+            if (P.slot_lin >= 0) P.meta[(row0 + r) * P.n_members + P.slot_lin] = member[2][r];
         }
-        RowResult res = finish_row(P, SVC, TREE_MODE != 0, has_lin, f_svc, raw[r], zl[r]);
-        store_row(P, row0 + r, res, !full);
-        po[2 * r] = (float)(1.0 - res.p1);
-        po[2 * r + 1] = (float)res.p1;
-        lab[r] = res.z > 0 ? 1 : 0;
-        if (res.uncertain || uncertain) fixmask |= 1u << r;
     }
     if (P.out && full) {                        // 4 rows x [p0, p1] = two 128-bit stores, 32 contiguous bytes per thread
         float4* o = reinterpret_cast<float4*>(P.out + 2 * row0);
         o[0] = make_float4(po[0], po[1], po[2], po[3]);
         o[1] = make_float4(po[4], po[5], po[6], po[7]);
     }
-    if (nonfinite) fixmask = (1u << R) - 1;     // the float64 path writes NaN for those rows and nothing else touches them
-    if (nonfinite) atomicOr(&s_nbad, 1u);
+    if (!full) fixmask &= (1u << (unsigned)max(0LL, min((long long)R, P.n - row0))) - 1u;
+    if (nonfinite) fixmask = full ? (1u << R) - 1 : fixmask | ((1u << (unsigned)max(0LL, min((long long)R, P.n - row0))) - 1u);
+    if (nonfinite) atomicOr(&s_nbad, 1u);       // the float64 path writes NaN for those rows
 
     // ---- per-block float64 re-evaluation of the flagged rows -----------------------------------------------------------
     __syncthreads();
     if (fixmask) {
 #pragma unroll
         for (int r = 0; r < R; ++r)
-            if ((fixmask >> r) & 1u)
-                if (row0 + r < P.n) s_fix[atomicAdd(&s_nfix, 1u)] = (unsigned short)(tid * R + r);
+            if ((fixmask >> r) & 1u) s_fix[atomicAdd(&s_nfix, 1u)] = (unsigned short)(tid * R + r);
     }
     __syncthreads();
     const unsigned nfix = s_nfix;

@@ -34,11 +34,13 @@ constexpr int F = HFE_N_FEATURES;
 constexpr int MAX_MEMBERS = 4;
 constexpr int MAX_SPLITS = 128;       // merged stump table capacity (kernel parameter space)
 constexpr int SV_GROUP = 4;           // support vectors per inner tile
-constexpr int SV_STEPS = F + 1;       // table steps per group: F weight steps + one folded-coefficient step
-constexpr int SV_ROWS = 2 * SV_STEPS; // float4 rows per group: each step is (w0,w0,w1,w1),(w2,w2,w3,w3) for FFMA2
-constexpr int SV_PAD_ROWS = 4;        // zero rows after the table so the 2-step-ahead prefetch may over-read
+constexpr int SV_STEPS = F + 1;       // float4 steps per group: F weight steps + one folded-coefficient step
+constexpr int SV_PAD_ROWS = 2;        // zero steps after the table so the 2-step-ahead prefetch may over-read
 constexpr int MAX_EDGES = 16;          // coupling-solver discontinuities (6 exist for eps = 0.0025)
-constexpr int SV_CHUNK = 8;           // float32 partial sums are folded into float64 every SV_CHUNK vectors
+#ifndef HFE_SV_CHUNK
+#define HFE_SV_CHUNK 4
+#endif
+constexpr int SV_CHUNK = HFE_SV_CHUNK;           // float32 partial sums are folded into float64 every SV_CHUNK vectors
 
 enum MemberKind { KIND_NONE = 0, KIND_SVC = 1, KIND_GBT = 2, KIND_LIN = 3 };
 
@@ -60,15 +62,16 @@ struct ScoreParams {
     unsigned long long* score;  // [1] or null
     unsigned int* status;       // [HFE_STATUS_WORDS]
     // SVC member
-    const float4* sv_tab;       // [n_groups][SV_ROWS] float4 (+ SV_PAD_ROWS of zeros)
+    const float4* sv_tab;       // [n_groups][SV_STEPS] float4: step d = weight d of 4 vectors (+ SV_PAD_ROWS zeros)
     const double* sv64;         // [n_sv][F] original order
     const double* dual64;       // [n_sv]
     int n_groups;               // multiple of SV_CHUNK / SV_GROUP
     int n_sv;
-    double mean[F], inv_scale[F], scale[F];
+    double mean[F], scale[F];
+    float mean_hi[F], mean_lo[F], inv_scale32[F];   // mean = hi + lo in float32; 1/scale rounded once
     double c_log2;              // gamma * log2(e)
     double gamma, svc_intercept, prob_a, prob_b;
-    double zz_limit;            // rows with c|z|^2 above this go to the float64 path (float32 2^x range)
+    double zz_limit;            // rows with gamma*|z|^2 above this go to the float64 path (float32 2^x range)
     double solver_guard;        // Platt argument within this of a solver edge => the solver's branch is uncertain
     double edges[MAX_EDGES];    // values of t = f*A+B where the coupling solver's sweep count changes
     int n_edges;
@@ -282,7 +285,9 @@ inline int build_svc(Model* m, const ParsedBlob& pb, uint32_t idx) {
         if (scale->f64()[d] == 0.0) return fail(HFE_ERR_BAD_BLOB, "blob: scaler scale_ holds a zero");
         P.mean[d] = mean->f64()[d];
         P.scale[d] = scale->f64()[d];
-        P.inv_scale[d] = 1.0 / scale->f64()[d];
+        P.mean_hi[d] = (float)P.mean[d];
+        P.mean_lo[d] = (float)(P.mean[d] - (double)P.mean_hi[d]);
+        P.inv_scale32[d] = (float)(1.0 / P.scale[d]);
     }
     P.gamma = gamma;
     P.c_log2 = gamma * 1.4426950408889634074;
@@ -307,7 +312,7 @@ inline int build_svc(Model* m, const ParsedBlob& pb, uint32_t idx) {
     }
     int padded = ((n_sv + SV_CHUNK - 1) / SV_CHUNK) * SV_CHUNK;
     int n_groups = padded / SV_GROUP;
-    std::vector<float4> tab((size_t)n_groups * SV_ROWS + SV_PAD_ROWS, make_float4(0.f, 0.f, 0.f, 0.f));
+    std::vector<float4> tab((size_t)n_groups * SV_STEPS + SV_PAD_ROWS, make_float4(0.f, 0.f, 0.f, 0.f));
     double max_norm = 0, coef_l2 = 0;
     for (int k = 0; k < n_sv; ++k) {
         int j = order[k];
@@ -316,19 +321,14 @@ inline int build_svc(Model* m, const ParsedBlob& pb, uint32_t idx) {
         for (int d = 0; d < F; ++d) ss += s[d] * s[d];
         max_norm = std::max(max_norm, std::sqrt(ss));
         coef_l2 += coef[j] * coef[j];
-        // step d of a group = two float4: (w0,w0,w1,w1) and (w2,w2,w3,w3); every value is stored twice so that one
-        // 64-bit register pair feeds a packed FFMA2 against a pair of rows
-        float* base = reinterpret_cast<float*>(&tab[(size_t)(k / SV_GROUP) * SV_ROWS]);
+        float* base = reinterpret_cast<float*>(&tab[(size_t)(k / SV_GROUP) * SV_STEPS]);
         int lane = k % SV_GROUP;
-        for (int d = 0; d <= F; ++d) {
-            float v = d < F ? (float)(2.0 * P.c_log2 * s[d]) : (float)(coef[j] * std::exp2(-P.c_log2 * ss));
-            base[d * 8 + lane * 2] = v;
-            base[d * 8 + lane * 2 + 1] = v;
-        }
+        for (int d = 0; d < F; ++d) base[d * 4 + lane] = (float)(2.0 * P.c_log2 * s[d]);
+        base[F * 4 + lane] = (float)(coef[j] * std::exp2(-P.c_log2 * ss));
     }
     // float32 2^x must not overflow: 2c|z||s| <= 100  =>  c|z|^2 <= c*(100/(2c*max|s|))^2
     double zmax = 100.0 / (2.0 * P.c_log2 * std::max(max_norm, 1e-30));
-    P.zz_limit = std::min(P.c_log2 * zmax * zmax, 900.0);
+    P.zz_limit = std::min(gamma * zmax * zmax, 600.0);          // compared against gamma*|z|^2
     // assumed uncertainty of the float32 decision value (DESIGN.md "error budget"): ~20 sigma of the measured error
     m->svc_guard = 3.5e-7 * std::sqrt(coef_l2) + 1e-7;
     P.n_groups = n_groups;
