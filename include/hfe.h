@@ -15,10 +15,17 @@
  *     only enqueue work: they neither allocate nor synchronise.
  *   - feature matrices are COLUMN-major float32: feature f of row i lives at x[f*ld + i], ld >= n, ld % 4 == 0 and x
  *     16-byte aligned so that a thread can fetch four consecutive rows of one column with one 128-bit load.
- *   - `status` is a device array of HFE_STATUS_WORDS uint32 that the call zeroes and then fills:
- *       [0] error bits (HFE_ROW_NONFINITE if any input value was NaN/Inf -- scikit-learn raises ValueError there,
- *           SK/svm/_base.py:652-660), [1] number of rows that were re-evaluated in float64 (see DESIGN.md,
- *           "guard bands"), [2..3] reserved.
+ *   - `status` is a device array of HFE_STATUS_WORDS uint32 (256 KiB) owned by the caller; the call zeroes its header
+ *     and then fills it:
+ *       [0] error bits: HFE_ROW_NONFINITE if any input value was NaN/Inf (scikit-learn raises ValueError there,
+ *           SK/svm/_base.py:652-660); HFE_WORKLIST_OVERFLOW if more than HFE_WORKLIST_CAPACITY rows needed the float64
+ *           re-evaluation (then the rows beyond the capacity keep their float32-path result: rerun the batch through
+ *           hfe_predict_proba_f64, as the Python facade does);
+ *       [1] number of rows that were re-evaluated in float64 ("guard bands");
+ *       [2] work-list length, [3] reserved, [4..] the work list itself (row indices).  The work list is scratch
+ *           memory of the call: the fused kernel appends the rows whose result hinges on a branch (coupling-solver
+ *           exit test, label sign), a second small kernel re-evaluates exactly those rows in float64.
+ *     Two calls that overlap on the device must not share a status array.  n must be < 2^32 rows per call.
  *   - a model handle is immutable after creation and may be shared by host threads and streams.
  */
 #ifndef HFE_H_
@@ -42,8 +49,12 @@ typedef enum hfe_status {
 } hfe_status;
 
 #define HFE_N_FEATURES 17          /* load_data_public.py schema after feature selection; predict_hf.py:6-26 */
-#define HFE_STATUS_WORDS 4
+#define HFE_STATUS_HEADER_WORDS 4
+#define HFE_WORKLIST_CAPACITY 65532   /* rows one call can hand to the float64 re-evaluation */
+#define HFE_STATUS_WORDS (HFE_STATUS_HEADER_WORDS + HFE_WORKLIST_CAPACITY)   /* 65536 uint32 = 256 KiB */
+#define HFE_STATUS_LIST_LEN 2
 #define HFE_ROW_NONFINITE 1u
+#define HFE_WORKLIST_OVERFLOW 2u
 
 typedef struct hfe_model hfe_model;
 

@@ -10,8 +10,11 @@ LIB_PATH = os.environ.get("HFE_LIB") or os.path.join(_HERE, "libhfe.so")   # HFE
 
 HFE_OK = 0
 HFE_ERR_NONFINITE_INPUT = 5
-STATUS_WORDS = 4
+STATUS_HEADER_WORDS = 4
+WORKLIST_CAPACITY = 65532
+STATUS_WORDS = STATUS_HEADER_WORDS + WORKLIST_CAPACITY      # 65536 uint32 = 256 KiB per call
 ROW_NONFINITE = 1
+WORKLIST_OVERFLOW = 2
 
 EXPORTS = [
     "hfe_abi_version", "hfe_last_error_string", "hfe_model_create", "hfe_model_destroy", "hfe_model_get_info",

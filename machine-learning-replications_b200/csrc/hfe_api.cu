@@ -1,6 +1,7 @@
 // hfe_api.cu -- the extern "C" boundary declared in include/hfe.h.  Plain pointers and sizes in, status codes out.
 #include <cstdio>
 #include <cstdlib>
+#include <map>
 #include <mutex>
 #include <new>
 
@@ -21,30 +22,40 @@ int check_matrix(const hfe_model* model, const float* x, int64_t n, int64_t ld) 
     if (ld < n) return fail(HFE_ERR_INVALID_ARGUMENT, "leading dimension smaller than the row count");
     if ((ld & 3) || (reinterpret_cast<uintptr_t>(x) & 15))
         return fail(HFE_ERR_INVALID_ARGUMENT, "feature matrix must be 16-byte aligned with ld % 4 == 0");
-    if (n > (int64_t)2147483647 * 256) return fail(HFE_ERR_TOO_LARGE, "more rows than one launch can address");
+    if (n >= ((int64_t)1 << 32)) return fail(HFE_ERR_TOO_LARGE, "at most 2^32 - 1 rows per call");
     return HFE_OK;
 }
 
 template <bool SVC, int TM>
 int launch_score(const Model* m, const ScoreParams& P, cudaStream_t stream) {
-    size_t sv_bytes = 0;
-    int smem_groups = 0;
-    if (SVC) {
-        smem_groups = std::min(P.n_groups, TM == 2 ? 128 : MAX_SMEM_GROUPS);
-        sv_bytes = ((size_t)smem_groups * SV_STEPS + SV_PAD_ROWS) * sizeof(float4);
-    }
-    size_t smem = sv_bytes + (TM == 2 ? (size_t)F * BLOCK_ROWS * sizeof(float) : 0);
+    if (SVC && P.n_groups > MAX_SMEM_GROUPS)
+        return fail(HFE_ERR_UNSUPPORTED, "more than 1536 support vectors do not fit one block's shared memory");
+    size_t smem = (SVC ? ((size_t)P.n_groups * SV_STEPS + SV_PAD_ROWS) * sizeof(float4) : 0) +
+                  (TM == 2 ? (size_t)F * BLOCK_ROWS * sizeof(float) : 0);
     auto kernel = hfe_score_kernel<SVC, TM>;
-    static std::once_flag once[16];        // per device: opt in to large dynamic shared memory once
-    static cudaError_t attr_err[16];
-    int dev = m->device & 15;
-    std::call_once(once[dev], [&] {
-        attr_err[dev] = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024);
-    });
-    if (attr_err[dev] != cudaSuccess)
-        return fail(HFE_ERR_CUDA, std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(attr_err[dev]));
-    long long blocks = (P.n + BLOCK_ROWS - 1) / BLOCK_ROWS;
-    kernel<<<(unsigned)blocks, BLOCK_THREADS, smem, stream>>>(P, smem_groups);
+    // per device and shared-memory size: opt in to large dynamic shared memory, ask how many blocks stay resident
+    static std::mutex mu;
+    static std::map<std::pair<int, size_t>, int> resident;
+    int per_sm = 0, sms = 0;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        auto key = std::make_pair(m->device, smem);
+        auto it = resident.find(key);
+        if (it == resident.end()) {
+            HFE_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+            HFE_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, BLOCK_THREADS, smem));
+            if (per_sm < 1) return fail(HFE_ERR_UNSUPPORTED, "model tables do not fit one SM's shared memory");
+            resident[key] = per_sm;
+        } else {
+            per_sm = it->second;
+        }
+    }
+    HFE_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, m->device));
+    // persistent blocks: every warp walks its own sequence of 128-row tiles
+    long long tiles = (P.n + WARP_ROWS - 1) / WARP_ROWS;
+    long long blocks = (tiles + BLOCK_WARPS - 1) / BLOCK_WARPS;
+    if (HFE_PERSISTENT) blocks = std::min<long long>(blocks, (long long)sms * per_sm);
+    kernel<<<(unsigned)blocks, BLOCK_THREADS, smem, stream>>>(P, P.n_groups);
     HFE_CUDA_TRY(cudaGetLastError());
     return HFE_OK;
 }
@@ -75,7 +86,7 @@ int score_common(const hfe_model* model, const float* x, int64_t n, int64_t ld, 
     const Model* m = model->impl;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     HFE_CUDA_TRY(cudaSetDevice(m->device));
-    HFE_CUDA_TRY(cudaMemsetAsync(status, 0, HFE_STATUS_WORDS * sizeof(uint32_t), s));
+    HFE_CUDA_TRY(cudaMemsetAsync(status, 0, HFE_STATUS_HEADER_WORDS * sizeof(uint32_t), s));
     if (n == 0) return HFE_OK;
     ScoreParams P = m->base;
     P.x = x;
@@ -97,7 +108,11 @@ int score_common(const hfe_model* model, const float* x, int64_t n, int64_t ld, 
         HFE_CUDA_TRY(cudaGetLastError());
         return HFE_OK;
     }
-    return dispatch_score(m, P, s);
+    rc = dispatch_score(m, P, s);
+    if (rc) return rc;
+    hfe_fixup_kernel<<<148, BLOCK_THREADS, 0, s>>>(P);       // re-evaluates the rows the fused kernel put on the work list
+    HFE_CUDA_TRY(cudaGetLastError());
+    return HFE_OK;
 }
 
 }  // namespace
@@ -110,7 +125,7 @@ int ingest_common(const T* x_rowmajor, int64_t n, int32_t n_features, float* x, 
         return fail(HFE_ERR_INVALID_ARGUMENT, "bad ingest sizes");
     if (!status) return fail(HFE_ERR_INVALID_ARGUMENT, "null status array");
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    HFE_CUDA_TRY(cudaMemsetAsync(status, 0, HFE_STATUS_WORDS * sizeof(uint32_t), s));
+    HFE_CUDA_TRY(cudaMemsetAsync(status, 0, HFE_STATUS_HEADER_WORDS * sizeof(uint32_t), s));
     if (n == 0) return HFE_OK;
     if (!x_rowmajor || !x) return fail(HFE_ERR_INVALID_ARGUMENT, "null ingest buffer");
     long long blocks = (n + BLOCK_THREADS - 1) / BLOCK_THREADS;
@@ -258,7 +273,9 @@ int hfe_predict_host(const hfe_model* model, const double* x_rowmajor, int64_t n
     size_t meta_bytes = meta ? (size_t)n * m->n_members * sizeof(double) : 0;
     size_t lab_bytes = labels ? (size_t)n : 0;
     auto up = [](size_t b) { return (b + 255) & ~(size_t)255; };
-    size_t total = up(in_bytes) + up(col_bytes) + up(out_bytes) + up(dec_bytes) + up(meta_bytes) + up(lab_bytes) + 256;
+    size_t status_bytes = (HFE_STATUS_WORDS + HFE_STATUS_HEADER_WORDS) * sizeof(uint32_t);
+    size_t total = up(in_bytes) + up(col_bytes) + up(out_bytes) + up(dec_bytes) + up(meta_bytes) + up(lab_bytes) +
+                   up(status_bytes) + 256;
     unsigned char* buf = nullptr;
     HFE_CUDA_TRY(cudaMalloc(&buf, total));
     struct Guard { unsigned char* p; ~Guard() { cudaFree(p); } } guard{buf};
@@ -270,24 +287,35 @@ int hfe_predict_host(const hfe_model* model, const double* x_rowmajor, int64_t n
     double* d_dec = decision ? reinterpret_cast<double*>(take(dec_bytes)) : nullptr;
     double* d_meta = meta ? reinterpret_cast<double*>(take(meta_bytes)) : nullptr;
     uint8_t* d_lab = labels ? take(lab_bytes) : nullptr;
-    uint32_t* d_status = reinterpret_cast<uint32_t*>(take(2 * HFE_STATUS_WORDS * sizeof(uint32_t)));
+    uint32_t* d_status = reinterpret_cast<uint32_t*>(take(status_bytes));   // [ingest header | scoring status]
     cudaStream_t s = nullptr;
     HFE_CUDA_TRY(cudaMemcpyAsync(d_in, x_rowmajor, in_bytes, cudaMemcpyHostToDevice, s));
     int rc = hfe_ingest_rowmajor_f64(d_in, n, F, d_x, ld, d_status, s);
     if (rc) return rc;
     rc = score_common(model, d_x, n, ld, -1, nullptr, d_out, nullptr, d_lab, d_dec, d_meta, nullptr, nullptr,
-                      d_status + HFE_STATUS_WORDS, s, false);
+                      d_status + HFE_STATUS_HEADER_WORDS, s, false);
     if (rc) return rc;
     std::vector<float> host_out((size_t)n * 2);
-    uint32_t host_status[2 * HFE_STATUS_WORDS];
+    uint32_t host_status[2 * HFE_STATUS_HEADER_WORDS];
     HFE_CUDA_TRY(cudaMemcpyAsync(host_out.data(), d_out, out_bytes, cudaMemcpyDeviceToHost, s));
     if (decision) HFE_CUDA_TRY(cudaMemcpyAsync(decision, d_dec, dec_bytes, cudaMemcpyDeviceToHost, s));
     if (meta) HFE_CUDA_TRY(cudaMemcpyAsync(meta, d_meta, meta_bytes, cudaMemcpyDeviceToHost, s));
     if (labels) HFE_CUDA_TRY(cudaMemcpyAsync(labels, d_lab, lab_bytes, cudaMemcpyDeviceToHost, s));
     HFE_CUDA_TRY(cudaMemcpyAsync(host_status, d_status, sizeof(host_status), cudaMemcpyDeviceToHost, s));
     HFE_CUDA_TRY(cudaStreamSynchronize(s));
-    if ((host_status[0] | host_status[HFE_STATUS_WORDS]) & HFE_ROW_NONFINITE)
+    if ((host_status[0] | host_status[HFE_STATUS_HEADER_WORDS]) & HFE_ROW_NONFINITE)
         return fail(HFE_ERR_NONFINITE_INPUT, "Input X contains NaN or infinity");
+    if (host_status[HFE_STATUS_HEADER_WORDS] & HFE_WORKLIST_OVERFLOW) {
+        // more rows than the work list holds needed float64: score the whole batch on the float64 path instead
+        rc = score_common(model, d_x, n, ld, -1, nullptr, d_out, nullptr, d_lab, d_dec, d_meta, nullptr, nullptr,
+                          d_status + HFE_STATUS_HEADER_WORDS, s, true);
+        if (rc) return rc;
+        HFE_CUDA_TRY(cudaMemcpyAsync(host_out.data(), d_out, out_bytes, cudaMemcpyDeviceToHost, s));
+        if (decision) HFE_CUDA_TRY(cudaMemcpyAsync(decision, d_dec, dec_bytes, cudaMemcpyDeviceToHost, s));
+        if (meta) HFE_CUDA_TRY(cudaMemcpyAsync(meta, d_meta, meta_bytes, cudaMemcpyDeviceToHost, s));
+        if (labels) HFE_CUDA_TRY(cudaMemcpyAsync(labels, d_lab, lab_bytes, cudaMemcpyDeviceToHost, s));
+        HFE_CUDA_TRY(cudaStreamSynchronize(s));
+    }
     if (proba_n2) {
         for (int64_t i = 0; i < n; ++i) {
             double p1 = (double)host_out[2 * i + 1];

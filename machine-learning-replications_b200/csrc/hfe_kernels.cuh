@@ -19,15 +19,18 @@
 namespace hfe {
 
 #ifndef HFE_BLOCK_THREADS
-#define HFE_BLOCK_THREADS 256
+#define HFE_BLOCK_THREADS 128
 #endif
 constexpr int BLOCK_THREADS = HFE_BLOCK_THREADS;
 constexpr int ROWS_PER_THREAD = 4;
 constexpr int BLOCK_ROWS = BLOCK_THREADS * ROWS_PER_THREAD;
 constexpr int MAX_SMEM_GROUPS = 384;      // support-vector groups staged per pass (384*18*16 B = 108 KB; 2 blocks/SM)
 constexpr int TREE_CHUNK = 16;            // float32 partial sums over trees are folded into float64 every 16 trees
+#ifndef HFE_PERSISTENT
+#define HFE_PERSISTENT 0                  // 1: resident blocks loop over tiles; 0: one 128-row tile per warp (measured faster)
+#endif
 #ifndef HFE_MIN_BLOCKS
-#define HFE_MIN_BLOCKS 2                  // resident blocks per SM the fused kernel is compiled for (128-register cap)
+#define HFE_MIN_BLOCKS 4                  // resident blocks per SM the fused kernel is compiled for (128-register cap)
 #endif
 
 __device__ __forceinline__ float ex2_approx(float x) {
@@ -79,17 +82,38 @@ __device__ __forceinline__ double exp_neg_fast(double x) {      // exp(x) for x 
     return __hiloint2double(__double2hiint(p) + (k << 20), __double2loint(p));   // p * 2^k, k >= -1010
 }
 
-// Platt + clamp + coupling + links + combiner for R rows at once, the R dependency chains interleaved.
+__device__ __forceinline__ double expit_fast(double x) {
+    double e = exp_neg_fast(-fabs(x));
+    double inv = rcp_fast(1.0 + e);
+    return x >= 0 ? inv : e * inv;
+}
+
+// Links of the members that do not depend on the RBF sum, and their share of the combiner's logit:
+// zpart = intercept + sum over {trees, logistic} of final_coef * P(class 1).
 template <int R>
-__device__ __forceinline__ void finish_rows_fast(const ScoreParams& P, bool has_svc, bool has_gbt, bool has_lin,
-                                                 const double (&f_svc)[R], const double (&raw)[R],
-                                                 const double (&zl)[R], double (&p1)[R], double (&zfin)[R],
-                                                 double (&member)[3][R], bool (&uncertain)[R]) {
+__device__ __forceinline__ void partial_logit_fast(const ScoreParams& P, bool has_gbt, bool has_lin,
+                                                   const double (&raw)[R], const double (&zl)[R], double (&zpart)[R],
+                                                   double (&member)[3][R]) {
 #pragma unroll
     for (int r = 0; r < R; ++r) {
-        uncertain[r] = false;
-        member[0][r] = member[1][r] = member[2][r] = 0.0;
+        member[0][r] = 0.0;
+        member[1][r] = has_gbt ? expit_fast(raw[r]) : 0.0;          // SK/_loss/loss.py:980-998
+        member[2][r] = has_lin ? expit_fast(zl[r]) : 0.0;           // SK/linear_model/_base.py:429-451
+        double z = P.final_intercept;
+        if (has_gbt) z = fma(P.final_coef[P.slot_gbt], member[1][r], z);
+        if (has_lin) z = fma(P.final_coef[P.slot_lin], member[2][r], z);
+        zpart[r] = z;
     }
+}
+
+// Platt + clamp + 2-class coupling for the SVC member, then the combiner, for R rows at once with the R dependency
+// chains interleaved.
+template <int R>
+__device__ __forceinline__ void finish_rows_fast(const ScoreParams& P, bool has_svc, const double (&f_svc)[R],
+                                                 const double (&zpart)[R], double (&p1)[R], double (&zfin)[R],
+                                                 double (&p_svc)[R], bool (&uncertain)[R]) {
+#pragma unroll
+    for (int r = 0; r < R; ++r) { uncertain[r] = false; p_svc[r] = 0.0; }
     if (has_svc) {
         double q00[R], q11[R], q01[R], iq00[R], iq11[R], a0[R], a1[R];
         bool done[R];
@@ -135,37 +159,14 @@ __device__ __forceinline__ void finish_rows_fast(const ScoreParams& P, bool has_
             if (all_done) break;
         }
 #pragma unroll
-        for (int r = 0; r < R; ++r) member[0][r] = a1[r];
-    }
-    if (has_gbt) {
-#pragma unroll
-        for (int r = 0; r < R; ++r) {
-            double e = exp_neg_fast(-fabs(raw[r]));
-            double inv = rcp_fast(1.0 + e);
-            member[1][r] = raw[r] >= 0 ? inv : e * inv;
-        }
-    }
-    if (has_lin) {
-#pragma unroll
-        for (int r = 0; r < R; ++r) {
-            double e = exp_neg_fast(-fabs(zl[r]));
-            double inv = rcp_fast(1.0 + e);
-            member[2][r] = zl[r] >= 0 ? inv : e * inv;
-        }
+        for (int r = 0; r < R; ++r) p_svc[r] = a1[r];
     }
 #pragma unroll
     for (int r = 0; r < R; ++r) {
-        double z = P.final_intercept;
-#pragma unroll
-        for (int slot = 0; slot < MAX_MEMBERS; ++slot) {              // estimators_ order
-            if (has_svc && slot == P.slot_svc) z = fma(P.final_coef[slot], member[0][r], z);
-            else if (has_gbt && slot == P.slot_gbt) z = fma(P.final_coef[slot], member[1][r], z);
-            else if (has_lin && slot == P.slot_lin) z = fma(P.final_coef[slot], member[2][r], z);
-        }
-        double e = exp_neg_fast(-fabs(z));
-        double inv = rcp_fast(1.0 + e);
+        double z = zpart[r];
+        if (has_svc) z = fma(P.final_coef[P.slot_svc], p_svc[r], z);
         zfin[r] = z;
-        p1[r] = z >= 0 ? inv : e * inv;
+        p1[r] = expit_fast(z);
         uncertain[r] = uncertain[r] || !(fabs(z) >= P.label_guard);
     }
 }
@@ -252,76 +253,77 @@ __device__ __forceinline__ int walk_tree(const ScoreParams& P, int t, XGet xget)
     return base + node;
 }
 
-// Cooperative float64 evaluation of one row by the whole block -- the exact-arithmetic path.  Follows the reference's
+// Cooperative float64 evaluation of one row by one warp -- the exact-arithmetic path.  Follows the reference's
 // operation order within each term (scale: SK/preprocessing/_data.py:1132-1134; kernel: svm.cpp:461-515); only the
-// order in which the n_sv kernel values / the trees are summed differs (strided partials + fixed-shape reduction).
-__device__ __noinline__ void eval_row_f64(const ScoreParams& P, long long row, double* s_x, double* s_z, double* s_red,
-                             unsigned int* s_hits) {
-    const int tid = threadIdx.x;
+// order in which the n_sv kernel values / the trees are summed differs (lane-strided partials + shuffle reduction).
+// All 32 lanes must call it together.  Lane f (< F) holds feature f of the row; other lanes fetch it by shuffle.
+// Returns (on every lane) whether the hard label equals y[row] when y is given.
+__device__ __noinline__ bool eval_row_f64_warp(const ScoreParams& P, long long row) {
+    const unsigned full_mask = 0xFFFFFFFFu;
+    const int lane = threadIdx.x & 31;
     const bool has_svc = P.slot_svc >= 0, has_gbt = P.slot_gbt >= 0, has_lin = P.slot_lin >= 0;
-    if (tid < F) {
-        float xv = load_feature(P, tid, row);
-        s_x[tid] = (double)xv;
-        s_z[tid] = ((double)xv - P.mean[tid]) / P.scale[tid];
-    }
-    __syncthreads();
+    float x_mine = lane < F ? load_feature(P, lane, row) : 0.f;
     double part_svc = 0.0, part_gbt = 0.0;
     if (has_svc) {
-        for (int j = tid; j < P.n_sv; j += BLOCK_THREADS) {
+        double z[F];
+#pragma unroll
+        for (int d = 0; d < F; ++d) z[d] = ((double)__shfl_sync(full_mask, x_mine, d) - P.mean[d]) / P.scale[d];
+        for (int j = lane; j < P.n_sv; j += 32) {
             const double* s = P.sv64 + (long long)j * F;
             double sum = 0.0;
 #pragma unroll
             for (int d = 0; d < F; ++d) {
-                double diff = s_z[d] - s[d];
+                double diff = z[d] - s[d];
                 sum += diff * diff;
             }
             part_svc += P.dual64[j] * exp(-P.gamma * sum);
         }
     }
     if (has_gbt) {
-        for (int t = tid; t < P.n_trees; t += BLOCK_THREADS) {
-            int leaf = walk_tree(P, t, [&](unsigned f) { return (float)s_x[f]; });
-            part_gbt += P.value64[leaf];
+        for (int t0 = 0; t0 < P.n_trees; t0 += 32) {          // uniform trip counts: every lane joins every shuffle
+            const int t = min(t0 + lane, P.n_trees - 1);
+            const int base = P.tree_off[t];
+            int node = 0;
+            for (int lvl = 0; lvl < P.max_depth; ++lvl) {       // leaves self-loop, so walking past a leaf is harmless
+                uint2 nd = __ldg(P.nodes + base + node);
+                float xv = __shfl_sync(full_mask, x_mine, (int)(nd.y >> 24));
+                node = (int)(nd.y & 0xFFFFFFu) + (xv > __uint_as_float(nd.x) ? 1 : 0);
+            }
+            if (t0 + lane < P.n_trees) part_gbt += P.value64[base + node];
         }
     }
-    // fixed-shape reduction: lanes by shuffle, then warps in index order
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
-        part_svc += __shfl_down_sync(0xFFFFFFFFu, part_svc, o);
-        part_gbt += __shfl_down_sync(0xFFFFFFFFu, part_gbt, o);
+        part_svc += __shfl_down_sync(full_mask, part_svc, o);
+        part_gbt += __shfl_down_sync(full_mask, part_gbt, o);
     }
-    if ((tid & 31) == 0) {
-        s_red[(tid >> 5) * 2] = part_svc;
-        s_red[(tid >> 5) * 2 + 1] = part_gbt;
+    double zl = 0.0;
+    bool finite = true;
+#pragma unroll
+    for (int d = 0; d < F; ++d) {
+        float xd = __shfl_sync(full_mask, x_mine, d);
+        zl += (double)xd * P.lin_coef[d];
+        finite = finite && (fabsf(xd) <= 3.402823466e38f);
     }
-    __syncthreads();
-    if (tid == 0) {
-        double f_svc = 0.0, raw = 0.0, zl = P.lin_intercept;
-        for (int w = 0; w < BLOCK_THREADS / 32; ++w) {
-            f_svc += s_red[2 * w];
-            raw += s_red[2 * w + 1];
-        }
-        f_svc += P.svc_intercept;
-        raw += P.gbt_init;
-        if (has_lin) {
-            zl = 0.0;
-            for (int d = 0; d < F; ++d) zl += s_x[d] * P.lin_coef[d];
-            zl += P.lin_intercept;
-        }
-        RowResult r = finish_row(P, has_svc, has_gbt, has_lin, f_svc, raw, zl);
-        bool finite = true;
-        for (int d = 0; d < F; ++d) finite = finite && (fabs(s_x[d]) <= 3.4028234663852886e38);
+    zl += P.lin_intercept;
+    int label = 0;
+    if (lane == 0) {
+        RowResult r = finish_row(P, has_svc, has_gbt, has_lin, part_svc + P.svc_intercept, part_gbt + P.gbt_init, zl);
         if (!finite) {
             r.p1 = r.z = __longlong_as_double(0x7FF8000000000000LL);
             r.member[0] = r.member[1] = r.member[2] = r.p1;
         }
         store_row(P, row, r);
-        if (s_hits && P.y && P.score) *s_hits += ((r.z > 0 ? 1 : 0) == P.y[row]) ? 1u : 0u;
+        label = r.z > 0 ? 1 : 0;
     }
-    __syncthreads();
+    label = __shfl_sync(full_mask, label, 0);
+    return P.y ? (label == (int)P.y[row]) : false;
 }
 
 // ---- the fused pass ----------------------------------------------------------------------------------------------------
+
+constexpr int WARP_ROWS = 32 * ROWS_PER_THREAD;          // rows one warp scores per tile
+constexpr int BLOCK_WARPS = BLOCK_THREADS / 32;
 
 template <bool SVC, int TREE_MODE>
 __global__ void __launch_bounds__(BLOCK_THREADS, HFE_MIN_BLOCKS)
@@ -330,15 +332,28 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
     float4* s_sv = reinterpret_cast<float4*>(smem_raw);                       // [smem_groups][SV_STEPS] (+pad)
     float* s_xt = reinterpret_cast<float*>(smem_raw) +
                   (SVC ? ((size_t)smem_groups * SV_STEPS + SV_PAD_ROWS) * 4 : 0);             // [F][BLOCK_ROWS]
-    __shared__ double s_x[F], s_z[F], s_red[2 * BLOCK_THREADS / 32];
-    __shared__ unsigned int s_nfix, s_nbad, s_hits;
-    __shared__ unsigned short s_fix[BLOCK_ROWS];
 
     const int tid = threadIdx.x;
-    const long long row0 = ((long long)blockIdx.x * BLOCK_THREADS + tid) * ROWS_PER_THREAD;
+    const int lane = tid & 31;
+    const int n_tiles = (int)((P.n + WARP_ROWS - 1) / WARP_ROWS);
+    // The support-vector table is staged in shared memory once per block (the only block-level barrier); after that
+    // every warp scores its own 128-row tile(s) with no further block-level synchronisation.  With HFE_PERSISTENT the
+    // grid is sized to the resident block count and warps loop over tiles; measured on B200 the plain one-tile-per-warp
+    // grid is ~15 % faster (the hardware block scheduler staggers blocks better than a static tile assignment).
+    if (SVC) {
+        for (int i = tid; i < P.n_groups * SV_STEPS + SV_PAD_ROWS; i += BLOCK_THREADS)
+            s_sv[i] = (i < P.n_groups * SV_STEPS) ? __ldg(P.sv_tab + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        __syncthreads();
+    }
+#if HFE_PERSISTENT
+    for (int tile = blockIdx.x * BLOCK_WARPS + (tid >> 5); tile < n_tiles; tile += gridDim.x * BLOCK_WARPS) {
+#else
+    const int tile = blockIdx.x * BLOCK_WARPS + (tid >> 5);
+    if (tile < n_tiles) {
+#endif
+    const long long row0 = (long long)tile * WARP_ROWS + lane * ROWS_PER_THREAD;
     const bool has_lin = P.slot_lin >= 0;
     constexpr int R = ROWS_PER_THREAD;
-    if (tid == 0) { s_nfix = 0; s_nbad = 0; s_hits = 0; }
 
     // ---- load 4 rows x 17 features (128-bit loads; guarded scalar loads on the ragged tail / permuted column) ------
     float xv[F][R];
@@ -438,6 +453,18 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
 #pragma unroll
         for (int p = 0; p < R / 2; ++p) z2[f][p] = make_float2(zf[2 * p], zf[2 * p + 1]);
     }
+    // Links of the tree and logistic members now, so that only their share of the combiner's logit (one double per
+    // row) has to stay in registers across the RBF loop.
+    double zpart[R], member[3][R];
+    partial_logit_fast<R>(P, TREE_MODE != 0, has_lin, raw, zl, zpart, member);
+    if (P.meta) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            if (row0 + r >= P.n) continue;
+            if (P.slot_gbt >= 0) P.meta[(row0 + r) * P.n_members + P.slot_gbt] = member[1][r];
+            if (P.slot_lin >= 0) P.meta[(row0 + r) * P.n_members + P.slot_lin] = member[2][r];
+        }
+    }
 
     // ---- RBF sum: 4 support vectors x 4 rows per tile, packed FFMA2 ------------------------------------------------------
     // Each table step is one float4 = the weights of 4 support vectors for one feature (step F: their folded
@@ -450,88 +477,51 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
 #pragma unroll
     for (int r = 0; r < R; ++r) acc64[r] = 0.0;
     if (SVC) {
-        for (int g0 = 0; g0 < P.n_groups; g0 += smem_groups) {
-            const int ng = min(smem_groups, P.n_groups - g0);
-            __syncthreads();
-            for (int i = tid; i < ng * SV_STEPS + SV_PAD_ROWS; i += BLOCK_THREADS)
-                s_sv[i] = (i < ng * SV_STEPS) ? __ldg(P.sv_tab + (size_t)g0 * SV_STEPS + i)
-                                              : make_float4(0.f, 0.f, 0.f, 0.f);
-            __syncthreads();
+        {
+            const int ng = P.n_groups;
             const float4* tab = s_sv;
             float4 ring[3];
             ring[0] = tab[0]; ring[1] = tab[1];
-            float2 tprev[SV_GROUP][R / 2], acc2[R / 2];
-            float cprev[SV_GROUP];
-#pragma unroll
-            for (int q = 0; q < SV_GROUP; ++q) {
-                cprev[q] = 0.f;
-#pragma unroll
-                for (int p = 0; p < R / 2; ++p) tprev[q][p] = make_float2(-1000.f, -1000.f);   // exp2 -> 0
-            }
-#pragma unroll
-            for (int p = 0; p < R / 2; ++p) acc2[p] = make_float2(0.f, 0.f);
-
-            // exp2 + coefficient accumulate for element k (0..7) of the previous group: (q, p) = (k / 2, k % 2)
-            auto exp_acc = [&](int k) {
-                const int q = k >> 1, p = k & 1;
-                float2 e = make_float2(ex2_approx(tprev[q][p].x), ex2_approx(tprev[q][p].y));
-                acc2[p] = __ffma2_rn(e, make_float2(cprev[q], cprev[q]), acc2[p]);
-            };
-
 #pragma unroll 1
             for (int g = 0; g < ng; ++g) {
                 float2 t2[SV_GROUP][R / 2];
 #pragma unroll
                 for (int st = 0; st < SV_STEPS; ++st) {
-                    ring[(st + 2) % 3] = tab[st + 2];         // SV_STEPS % 3 == 0: same ring slot in every group
+                    ring[(st + 2) % 3] = tab[st + 2];
                     const float4 w4 = ring[st % 3];
                     const float w[SV_GROUP] = {w4.x, w4.y, w4.z, w4.w};
                     if (st == 0) {
 #pragma unroll
                         for (int p = 0; p < R / 2; ++p)
 #pragma unroll
-                            for (int q = 0; q < SV_GROUP; ++q)
-                                t2[q][p] = __fmul2_rn(z2[0][p], make_float2(w[q], w[q]));
+                            for (int q = 0; q < SV_GROUP; ++q) t2[q][p] = __fmul2_rn(z2[0][p], make_float2(w[q], w[q]));
                     } else if (st < F) {
 #pragma unroll
                         for (int p = 0; p < R / 2; ++p)
 #pragma unroll
                             for (int q = 0; q < SV_GROUP; ++q)
                                 t2[q][p] = __ffma2_rn(z2[st][p], make_float2(w[q], w[q]), t2[q][p]);
-                    }
-                    // previous group's exponentials, spread over steps 1,3,...,15
-                    if ((st & 1) && st < 2 * SV_GROUP * (R / 2)) exp_acc(st >> 1);
-                    if (st == F) {
+                    } else {
 #pragma unroll
-                        for (int q = 0; q < SV_GROUP; ++q) {
-                            cprev[q] = w[q];
+                        for (int p = 0; p < R / 2; ++p) {
+                            float2 a2 = make_float2(0.f, 0.f);
 #pragma unroll
-                            for (int p = 0; p < R / 2; ++p) tprev[q][p] = t2[q][p];
+                            for (int q = 0; q < SV_GROUP; ++q) {
+                                float2 e = make_float2(ex2_approx(t2[q][p].x), ex2_approx(t2[q][p].y));
+                                a2 = __ffma2_rn(e, make_float2(w[q], w[q]), a2);
+                            }
+                            acc64[2 * p] += (double)a2.x;
+                            acc64[2 * p + 1] += (double)a2.y;
                         }
                     }
                 }
                 tab += SV_STEPS;
-                // fold the float32 partial sums (4 vectors) into float64
-#pragma unroll
-                for (int p = 0; p < R / 2; ++p) {
-                    acc64[2 * p] += (double)acc2[p].x;
-                    acc64[2 * p + 1] += (double)acc2[p].y;
-                    acc2[p] = make_float2(0.f, 0.f);
-                }
-            }
-            // drain: the last group's exponentials
-#pragma unroll
-            for (int k = 0; k < SV_GROUP * (R / 2); ++k) exp_acc(k);
-#pragma unroll
-            for (int p = 0; p < R / 2; ++p) {
-                acc64[2 * p] += (double)acc2[p].x;
-                acc64[2 * p + 1] += (double)acc2[p].y;
             }
         }
     }
 
-    // ---- float64 epilogue: Platt, coupling, links, combiner (4 rows interleaved) ------------------------------------------
-    double f_svc[R], p1[R], zfin[R], member[3][R];
+    // ---- float64 epilogue: Platt, clamp, coupling, combiner (R rows interleaved) -------------------------------------------
+    double f_svc[R], p1[R], zfin[R];
     bool unc[R];
     unsigned fixmask = 0;
 #pragma unroll
@@ -543,7 +533,7 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
             if (!(gzz <= P.zz_limit)) fixmask |= 1u << r;               // float32 2^x range guard (or NaN)
         }
     }
-    finish_rows_fast<R>(P, SVC, TREE_MODE != 0, has_lin, f_svc, raw, zl, p1, zfin, member, unc);
+    finish_rows_fast<R>(P, SVC, f_svc, zpart, p1, zfin, member[0], unc);
     unsigned char lab[R];
     float po[2 * R];
 #pragma unroll
@@ -557,11 +547,7 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
         if (P.out64) { P.out64[2 * (row0 + r)] = 1.0 - p1[r]; P.out64[2 * (row0 + r) + 1] = p1[r]; }
         if (P.labels) P.labels[row0 + r] = lab[r];
         if (P.decision) P.decision[row0 + r] = zfin[r];
-        if (P.meta) {
-            if (P.slot_svc >= 0) P.meta[(row0 + r) * P.n_members + P.slot_svc] = member[0][r];
-            if (P.slot_gbt >= 0) P.meta[(row0 + r) * P.n_members + P.slot_gbt] = member[1][r];
-            if (P.slot_lin >= 0) P.meta[(row0 + r) * P.n_members + P.slot_lin] = member[2][r];
-        }
+        if (P.meta && P.slot_svc >= 0) P.meta[(row0 + r) * P.n_members + P.slot_svc] = member[0][r];
     }
     if (P.out && full) {                        // 4 rows x [p0, p1] = two 128-bit stores, 32 contiguous bytes per thread
         float4* o = reinterpret_cast<float4*>(P.out + 2 * row0);
@@ -570,45 +556,56 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
     }
     if (!full) fixmask &= (1u << (unsigned)max(0LL, min((long long)R, P.n - row0))) - 1u;
     if (nonfinite) fixmask = full ? (1u << R) - 1 : fixmask | ((1u << (unsigned)max(0LL, min((long long)R, P.n - row0))) - 1u);
-    if (nonfinite) atomicOr(&s_nbad, 1u);       // the float64 path writes NaN for those rows
 
-    // ---- per-block float64 re-evaluation of the flagged rows -----------------------------------------------------------
-    __syncthreads();
+    // ---- rows whose result hinges on a branch go to the work list; hfe_fixup_kernel re-evaluates them in float64 -------
     if (fixmask) {
 #pragma unroll
-        for (int r = 0; r < R; ++r)
-            if ((fixmask >> r) & 1u) s_fix[atomicAdd(&s_nfix, 1u)] = (unsigned short)(tid * R + r);
-    }
-    __syncthreads();
-    const unsigned nfix = s_nfix;
-    if (nfix) {
-        const long long block_row0 = (long long)blockIdx.x * BLOCK_ROWS;
-        for (unsigned i = 0; i < nfix; ++i) eval_row_f64(P, block_row0 + s_fix[i], s_x, s_z, s_red, &s_hits);
-        if (tid == 0) {
-            atomicAdd(P.status + 1, nfix);
-            if (s_nbad) atomicOr(P.status, HFE_ROW_NONFINITE);
+        for (int r = 0; r < R; ++r) {
+            if ((fixmask >> r) & 1u) {
+                unsigned slot = atomicAdd(P.status + HFE_STATUS_LIST_LEN, 1u);
+                if (slot < (unsigned)HFE_WORKLIST_CAPACITY) P.status[HFE_STATUS_HEADER_WORDS + slot] = (unsigned)(row0 + r);
+                else atomicOr(P.status, HFE_WORKLIST_OVERFLOW);
+            }
         }
     }
+    if (nonfinite) atomicOr(P.status, HFE_ROW_NONFINITE);
 
-    // ---- optional accuracy count for permutation importance (label vs y; flagged rows were counted by the f64 path) ----
-    if (P.y && P.score) {
+    if (P.y && P.score) {                                         // accuracy count; flagged rows are counted by the fix-up
         unsigned hits = 0;
 #pragma unroll
         for (int r = 0; r < R; ++r)
             if (row0 + r < P.n && !((fixmask >> r) & 1u)) hits += (lab[r] == P.y[row0 + r]) ? 1u : 0u;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) hits += __shfl_down_sync(0xFFFFFFFFu, hits, o);
-        if ((tid & 31) == 0 && hits) atomicAdd(&s_hits, hits);
-        __syncthreads();
-        if (tid == 0 && s_hits) atomicAdd(P.score, (unsigned long long)s_hits);
+        if (lane == 0 && hits) atomicAdd(P.score, (unsigned long long)hits);
+    }
+    }   // tile loop
+}
+
+// Second (tiny) launch of every scoring call: one warp per work-list entry re-evaluates that row in float64 and
+// overwrites the fused kernel's outputs for it.
+__global__ void __launch_bounds__(BLOCK_THREADS)
+hfe_fixup_kernel(const __grid_constant__ ScoreParams P) {
+    const unsigned count = min(P.status[HFE_STATUS_LIST_LEN], (unsigned)HFE_WORKLIST_CAPACITY);
+    const unsigned warp = (blockIdx.x * BLOCK_THREADS + threadIdx.x) >> 5;
+    const unsigned n_warps = (gridDim.x * BLOCK_THREADS) >> 5;
+    unsigned hits = 0;
+    for (unsigned i = warp; i < count; i += n_warps) {
+        bool hit = eval_row_f64_warp(P, (long long)P.status[HFE_STATUS_HEADER_WORDS + i]);
+        hits += hit ? 1u : 0u;
+    }
+    if ((threadIdx.x & 31) == 0) {
+        if (hits && P.score) atomicAdd(P.score, (unsigned long long)hits);
+        if (warp == 0) P.status[1] = count;
     }
 }
 
 // Every row through the float64 path (calibration / test aid; also what hfe_predict_proba_f64 runs).
 __global__ void __launch_bounds__(BLOCK_THREADS)
 hfe_score_f64_kernel(const __grid_constant__ ScoreParams P) {
-    __shared__ double s_x[F], s_z[F], s_red[2 * BLOCK_THREADS / 32];
-    for (long long row = blockIdx.x; row < P.n; row += gridDim.x) eval_row_f64(P, row, s_x, s_z, s_red, nullptr);
+    const long long warp = ((long long)blockIdx.x * BLOCK_THREADS + threadIdx.x) >> 5;
+    const long long n_warps = ((long long)gridDim.x * BLOCK_THREADS) >> 5;
+    for (long long row = warp; row < P.n; row += n_warps) eval_row_f64_warp(P, row);
 }
 
 // ---- GradientBoostingClassifier.apply ------------------------------------------------------------------------------------

@@ -91,6 +91,8 @@ struct ScoreParams {
     const int* tree_off;        // [n_trees+1]
     const unsigned char* tree_depth;  // [n_trees]
     const unsigned short* sk_id;      // scikit-learn node id per re-laid node
+    int max_depth;                    // deepest tree (uniform loop bound of the warp-cooperative float64 walk)
+    int pad_depth_;
     // logistic member
     double lin_coef[F];
     double lin_intercept;
@@ -458,6 +460,7 @@ inline int build_gbt(Model* m, const ParsedBlob& pb, uint32_t idx) {
     m->n_trees = n_trees;
     m->n_nodes = (int)n_nodes;
     m->max_depth = max_depth;
+    P.max_depth = max_depth;
     m->gbt_guard = 2.4e-7 * sum_max_abs + 1e-9;       // float32 leaf values and float32 partial sums
     if (all_stumps && (int)merged.size() <= MAX_SPLITS) {
         m->tree_mode = 1;

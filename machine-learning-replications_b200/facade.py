@@ -167,12 +167,13 @@ class HFStackB200:
         with torch.cuda.device(self.device):
             src = torch.from_numpy(arr).to(f"cuda:{self.device}")
             dst = torch.zeros((self.n_features_in_, ld), dtype=torch.float32, device=src.device)
-            status = torch.zeros(capi.STATUS_WORDS, dtype=torch.int32, device=src.device)
+            status = torch.zeros(capi.STATUS_HEADER_WORDS, dtype=torch.int32, device=src.device)
             capi.check(self._lib.hfe_ingest_rowmajor_f64(src.data_ptr(), n, self.n_features_in_, dst.data_ptr(), ld,
                                                          status.data_ptr(), self._stream()))
         return dst
 
     def new_status(self):
+        """Per-call status + work-list buffer (256 KiB of device memory; calls in flight at once need one each)."""
         import torch
         return torch.zeros(capi.STATUS_WORDS, dtype=torch.int32, device=f"cuda:{self.device}")
 
@@ -231,7 +232,7 @@ class HFStackB200:
                                    raw=torch.empty((chunk, self.n_features_in_), dtype=x_host.dtype, device=dev),
                                    col=torch.empty((self.n_features_in_, chunk), dtype=torch.float32, device=dev),
                                    out=torch.empty((chunk, 2), dtype=torch.float32, device=dev),
-                                   st_in=torch.zeros(capi.STATUS_WORDS, dtype=torch.int32, device=dev),
+                                   st_in=torch.zeros(capi.STATUS_HEADER_WORDS, dtype=torch.int32, device=dev),
                                    st=torch.zeros(capi.STATUS_WORDS, dtype=torch.int32, device=dev),
                                    flags=torch.zeros(1, dtype=torch.int32, device=dev)) for _ in range(2)]
             self._pipe_key = key
@@ -257,6 +258,17 @@ class HFStackB200:
             bad |= int(slot["flags"].item())
         if bad & capi.ROW_NONFINITE:
             raise ValueError("Input X contains NaN or infinity.")
+        if bad & capi.WORKLIST_OVERFLOW:
+            # more rows than one call's work list holds needed float64: redo the batch on the all-float64 path
+            slot = self._pipe[0]
+            for begin in range(0, n, chunk):
+                rows = min(chunk, n - begin)
+                slot["raw"][:rows].copy_(x_host[begin:begin + rows])
+                capi.check(ingest(slot["raw"].data_ptr(), rows, self.n_features_in_, slot["col"].data_ptr(), chunk,
+                                  slot["st_in"].data_ptr(), self._stream()))
+                o64 = self.predict_proba_f64_device(slot["col"], n=rows)
+                out_host[begin:begin + rows].copy_(o64.float())
+            torch.cuda.current_stream(self.device).synchronize()
         return out_host
 
     def predict_proba_f64_device(self, x, n=None, out=None, status=None):
