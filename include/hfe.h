@@ -132,6 +132,29 @@ int hfe_ingest_rowmajor_f32(const float* x_rowmajor, int64_t n, int32_t n_featur
 int hfe_predict_host(const hfe_model* model, const double* x_rowmajor, int64_t n, double* proba_n2, uint8_t* labels,
                      double* decision, double* meta);
 
+/* No counterpart in the reference (added for embedders; nothing in predict_hf.py / scikit-learn corresponds to it).
+ *
+ * hfe_predict_proba for callers that cannot obtain device memory of their own.  The ordinary entry points need a
+ * caller-supplied 256 KiB `status` array in device memory (error bits + the work list of rows that get re-evaluated
+ * in float64).  A caller that lives inside someone else's process -- a scoring plug-in in a database or an inference
+ * server that has already handed every byte of device memory to its own pool, or a service whose policy forbids any
+ * allocation once it is serving -- receives x and out_n2 from its host but has nowhere to take that array from and
+ * may not call cudaMalloc.  This entry point keeps the array inside the library instead: a fixed 256 KiB block of
+ * device memory that is part of the loaded library image on every GPU that loads it, for the life of the process.
+ * It calls no cudaMalloc / cudaFree and no allocating library routine.
+ *
+ *   - n may be at most HFE_NOALLOC_MAX_ROWS; larger batches are refused with HFE_ERR_TOO_LARGE (split them).
+ *   - flags (device pointer to one uint32, may be NULL) receives the error bits the `status[0]` word would hold.
+ *   - The first call on each device looks up the block's device address (cudaGetSymbolAddress); make that first call
+ *     outside any stream capture.  Later calls only enqueue work on `stream`.
+ *   - All calls on one GPU share the block.  Each call clears the counters it needs before use, so results never depend
+ *     on an earlier call, but two calls whose kernels overlap on the GPU (different streams, or different host
+ *     threads) would race on it: keep calls to this entry point on one stream per device, or serialise them.
+ */
+#define HFE_NOALLOC_MAX_ROWS 67108864   /* 2^26 rows per call */
+int hfe_predict_proba_noalloc(const hfe_model* model, const float* x, int64_t n, int64_t ld, float* out_n2,
+                              uint32_t* flags, void* stream);
+
 const char* hfe_last_error_string(void);
 int hfe_abi_version(void);
 

@@ -257,6 +257,54 @@ int hfe_ingest_rowmajor_f32(const float* x_rowmajor, int64_t n, int32_t n_featur
     return ingest_common(x_rowmajor, n, n_features, x, ld, status, stream);
 }
 
+// ---- allocation-free variant ------------------------------------------------------------------------------------------
+// Scratch for hfe_predict_proba_noalloc: the status header + work list that the fused kernel and the fix-up kernel
+// share, kept in the library image (256 KiB of device memory per GPU that loads this library) so that the call never
+// has to ask anyone for memory.  In host code this name is only a handle for cudaGetSymbolAddress -- it is not a
+// device address and must not be passed to a kernel as one.
+static __device__ __align__(256) unsigned int g_noalloc_scratch[HFE_STATUS_WORDS];
+
+namespace {
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_noalloc_mutex;
+unsigned int* g_noalloc_device_ptr[NOALLOC_MAX_DEVICES] = {nullptr};
+
+// Device address of g_noalloc_scratch on `device` (which must be current).  Looked up once per device.
+int noalloc_scratch(int device, unsigned int** out) {
+    if (device < 0 || device >= NOALLOC_MAX_DEVICES) return fail(HFE_ERR_INVALID_ARGUMENT, "device ordinal out of range");
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_device_ptr[device]) {
+        void* p = nullptr;
+        HFE_CUDA_TRY(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        g_noalloc_device_ptr[device] = static_cast<unsigned int*>(p);
+    }
+    *out = g_noalloc_device_ptr[device];
+    return HFE_OK;
+}
+}  // namespace
+
+int hfe_predict_proba_noalloc(const hfe_model* model, const float* x, int64_t n, int64_t ld, float* out_n2,
+                              uint32_t* flags, void* stream) {
+    if (!model || !model->impl) return fail(HFE_ERR_INVALID_ARGUMENT, "null model handle");
+    if (n > (int64_t)HFE_NOALLOC_MAX_ROWS)
+        return fail(HFE_ERR_TOO_LARGE, "hfe_predict_proba_noalloc scores at most HFE_NOALLOC_MAX_ROWS (2^26) rows per "
+                                       "call: split the batch");
+    if (n > 0 && !out_n2) return fail(HFE_ERR_INVALID_ARGUMENT, "null output");
+    HFE_CUDA_TRY(cudaSetDevice(model->impl->device));
+    unsigned int* scratch = nullptr;
+    int rc = noalloc_scratch(model->impl->device, &scratch);
+    if (rc) return rc;
+    // score_common clears the header words (error bits, work-list length) on `stream` before the kernels run, so
+    // whatever the previous call left in the block cannot leak into this one
+    rc = score_common(model, x, n, ld, -1, nullptr, out_n2, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr,
+                      scratch, stream, false);
+    if (rc) return rc;
+    if (flags)
+        HFE_CUDA_TRY(cudaMemcpyAsync(flags, scratch, sizeof(uint32_t), cudaMemcpyDeviceToDevice,
+                                     static_cast<cudaStream_t>(stream)));
+    return HFE_OK;
+}
+
 int hfe_predict_host(const hfe_model* model, const double* x_rowmajor, int64_t n, double* proba_n2, uint8_t* labels,
                      double* decision, double* meta) {
     if (!model || !model->impl) return fail(HFE_ERR_INVALID_ARGUMENT, "null model handle");
