@@ -41,15 +41,35 @@ METRIC = "patient-rows/sec ensemble predict_proba"
 
 
 def load_model(name):
+    """(package, ModelArrays, column specs of the synthetic rows) for a --model choice."""
     pkg = importlib.import_module("machine-learning-replications_b200")
-    path = os.path.join(GOLDEN, f"{name}_model.blob")
-    arrays = pkg.export.read_blob(open(path, "rb").read())
-    if name == "published":
+    base = "retrained" if name == "retrained" else "published"
+    arrays = pkg.export.read_blob(open(os.path.join(GOLDEN, f"{base}_model.blob"), "rb").read())
+    if base == "published":
         specs = pkg.synth.schema_specs()
     else:
         cand = pkg.synth.candidate_specs()
         specs = [cand[c] for c in np.load(os.path.join(GOLDEN, "retrained_columns.npy"))]
-    return pkg, path, arrays, specs
+    if name == "published_nosvc":          # the members that are genuinely HBM-bound (SURVEY.md section 8d)
+        arrays = pkg.synth_models.without_member(arrays, "svc")
+    elif name == "stress":                 # BASELINE.json config 4: 2000 trees, depth 16, node tables >> shared memory
+        arrays = pkg.synth_models.stress_stack(arrays, with_svc=False)
+    elif name == "stress_svc":
+        arrays = pkg.synth_models.stress_stack(arrays, with_svc=True)
+    return pkg, arrays, specs
+
+
+def describe(arrays):
+    parts = []
+    for m in arrays.members:
+        if m.kind == "svc":
+            parts.append(f"scaler+RBF-SVC {m.sv.shape[0]} SVs")
+        elif m.kind == "gbt":
+            nodes = sum(t.left.shape[0] for t in m.trees)
+            parts.append(f"{len(m.trees)} boosted trees ({nodes} nodes)")
+        else:
+            parts.append("L1 logistic")
+    return " + ".join(parts) + " -> logistic combiner"
 
 
 def measured_peaks():
@@ -128,7 +148,7 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", 0))
     if rank != 0:
         return
-    pkg, _, arrays, specs = load_model(args.model)
+    pkg, arrays, specs = load_model(args.model)
     cores = len(os.sched_getaffinity(0))
     sample = int(args.cpu_rows or min(max(20000 * cores, 20000), 2_000_000))
     times = []
@@ -142,8 +162,9 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": value, "unit": "rows/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"{args.model} stack, scikit-learn predict_proba on host cores",
-                   "rows_per_step": sample, "model": args.model},
+        "config": {"workload": f"{args.model} stack ({describe(arrays)}), synthetic patient rows, predict_proba",
+                   "model": args.model, "rows_per_step": sample,
+                   "note": "bounded sample of the same workload on the host cores (scikit-learn, the reference path)"},
         "cpu_baseline": {"value": value, "unit": "rows/s", "cores": cores, "kind": "reference",
                          "sample": f"{sample} synthetic rows per step, joblib threads over {cores} cores, "
                                    "scikit-learn 1.9 StackingClassifier.predict_proba rebuilt from the same arrays"},
@@ -156,7 +177,7 @@ def run_reference(args):
 def run_ours(args):
     import torch
 
-    pkg, blob_path, arrays, specs = load_model(args.model)
+    pkg, arrays, specs = load_model(args.model)
     shard = pkg.shard
     rank, local_rank, world = shard.init_process_group()
     if world != args.gpus:
@@ -165,7 +186,7 @@ def run_ours(args):
         raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback for the scoring path")
     torch.cuda.set_device(local_rank)
     dev = f"cuda:{local_rank}"
-    clf = pkg.HFStackB200.from_blob_file(blob_path, device=local_rank)
+    clf = pkg.HFStackB200.from_arrays(arrays, device=local_rank)
     rows = int(args.rows)
     n_total = rows * world
     begin, end = shard.shard_range(n_total, rank, world)
@@ -230,7 +251,7 @@ def run_ours(args):
     avg_launch_ms = sum(per_launch) / len(per_launch)
     achieved = BYTES_PER_ROW * n / (avg_launch_ms * 1e-3) / 1e9
     n_sv = int(clf.info.n_support_vectors)
-    n_sv_pad = (n_sv + 7) // 8 * 8
+    n_sv_pad = (n_sv + 3) // 4 * 4
     fma_per_row = n_sv_pad * 18                      # 17-term dot + coefficient accumulate per support vector
     sm_mhz = (clocks or {}).get("sm_mhz") or sm_max
     fma_peak = 148 * 128 * sm_mhz * 1e6
@@ -245,8 +266,7 @@ def run_ours(args):
         "metric": METRIC, "value": value, "unit": "rows/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{args.model} stack (scaler+RBF-SVC {n_sv} SVs, {int(clf.info.n_trees)} boosted stumps, "
-                               f"L1 logistic, logistic combiner), {rows} synthetic patient rows per GPU, predict_proba",
+        "config": {"workload": f"{args.model} stack ({describe(arrays)}), synthetic patient rows, predict_proba",
                    "model": args.model, "rows_per_gpu": rows, "rows_total": n_total, "layout": "column-major f32 [17][n]",
                    "l2": "inputs larger than L2 (680 MB per pass vs 126 MB)", "f64_reevaluated_rows_last_step": fixups},
         "clocks": clocks,
@@ -254,17 +274,19 @@ def run_ours(args):
                 "d2h_bytes_per_step": e2e_rows * 2 * 4, "rows_per_step": e2e_rows, "steps": e2e_steps,
                 "api": "HFStackB200.predict_proba_pinned (H2D + ingest + fused kernel + D2H, 2 streams)",
                 "max_abs_diff_vs_device_path": e2e_check},
-        "gpu_launches": args.steps * world,
+        "gpu_launches": 2 * args.steps * world,      # fused pass + work-list fix-up per step and rank
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                      "frac": achieved / hbm_peak, "traffic": traffic, "peak_source": peak_src,
-                     "kernel": "hfe_score_kernel<SVC,stumps>", "bytes_per_row": BYTES_PER_ROW,
-                     "avg_launch_ms": avg_launch_ms,
-                     "note": "the RBF-SVC member makes this pass FP32-issue bound, not HBM bound: see fma_roofline"},
-        "fma_roofline": {"bound": "fp32 fma pipe", "achieved": fma_per_row * n / (avg_launch_ms * 1e-3) / 1e12,
-                         "peak": fma_peak / 1e12, "unit": "T lane-FMA/s", "frac":
-                         fma_per_row * n / (avg_launch_ms * 1e-3) / fma_peak, "fma_per_row": fma_per_row,
-                         "sm_mhz_used": sm_mhz},
+                     "kernel": "hfe_score_kernel (fused pass; the work-list fix-up launch that follows takes microseconds)",
+                     "bytes_per_row": BYTES_PER_ROW, "avg_launch_ms": avg_launch_ms,
+                     "note": ("the RBF-SVC member makes this pass FP32-FMA bound, not HBM bound: see fma_roofline"
+                              if n_sv else "no SVC member: this configuration is the HBM-bound part of the ensemble")},
     }
+    if n_sv:
+        line["fma_roofline"] = {"bound": "fp32 fma pipe", "achieved": fma_per_row * n / (avg_launch_ms * 1e-3) / 1e12,
+                                "peak": fma_peak / 1e12, "unit": "T lane-FMA/s",
+                                "frac": fma_per_row * n / (avg_launch_ms * 1e-3) / fma_peak,
+                                "fma_per_row": fma_per_row, "sm_mhz_used": sm_mhz}
     if world == 1 and not args.no_cpu:
         cores = len(os.sched_getaffinity(0))
         sample = int(args.cpu_rows or min(max(20000 * cores, 20000), 2_000_000))
@@ -281,7 +303,8 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--rows", type=int, default=10_000_000, help="rows per GPU per step")
-    ap.add_argument("--model", default="retrained", choices=["retrained", "published"])
+    ap.add_argument("--model", default="retrained",
+                    choices=["retrained", "published", "published_nosvc", "stress", "stress_svc"])
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--e2e-rows", type=int, default=10_000_000)
     ap.add_argument("--cpu-rows", type=int, default=0)
