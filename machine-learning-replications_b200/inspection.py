@@ -1,0 +1,69 @@
+"""Permutation feature importance on the device (BASELINE.json config 5).
+
+Same procedure as ``sklearn.inspection.permutation_importance`` (SK/inspection/_permutation_importance.py:31-76,
+278-313) with its default scorer for classifiers (accuracy): one ``random_seed`` is drawn from ``random_state`` and
+*every* column restarts a ``RandomState(random_seed)``, shuffles an index vector cumulatively ``n_repeats`` times,
+applies it each time to the already permuted column, and scores the matrix.  Here the ``n_repeats`` index vectors are made
+once on the host (so they are exactly scikit-learn's), uploaded as int32, and each (column, repeat) pass is one launch
+of the fused kernel with ``perm_col`` / ``perm_idx`` -- the shuffled matrix is never materialised -- and an on-device
+count of ``label == y``.  With several ranks the 17 x n_repeats passes are dealt round-robin and the counts are summed
+with one all-reduce of 86 integers; every rank holds the full matrix (1 M rows = 68 MB).
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+class ImportanceResult(dict):
+    """``importances_mean``, ``importances_std``, ``importances`` like scikit-learn's Bunch, plus ``baseline_score``."""
+    __getattr__ = dict.__getitem__
+
+
+def shuffled_indices(n_samples: int, n_repeats: int, random_seed: int) -> np.ndarray:
+    """Row r = where the permuted column's values come from at repeat r.  scikit-learn keeps shuffling one index vector
+    and applies it to the *already permuted* column (``X_permuted[:, j] = X_permuted[shuffling_idx, j]``,
+    SK/inspection/_permutation_importance.py:66-74), so the effective source index composes: e_r = e_{r-1}[s_r]."""
+    rng = np.random.RandomState(random_seed)
+    idx = np.arange(n_samples)
+    eff = np.arange(n_samples)
+    out = np.empty((n_repeats, n_samples), dtype=np.int32)
+    for r in range(n_repeats):
+        rng.shuffle(idx)
+        eff = eff[idx]
+        out[r] = eff
+    return out
+
+
+def permutation_importance(clf, x, y, n_repeats: int = 5, random_state=None, rank: int = 0, world: int = 1):
+    """``x``: column-major float32 CUDA tensor ``[17, ld]`` (or a numpy ``[n,17]`` array), ``y``: class labels.
+    Returns an ``ImportanceResult``; with ``world > 1`` torch.distributed must be initialised."""
+    import torch
+
+    if isinstance(x, np.ndarray):
+        n = x.shape[0]
+        x = clf.to_device_colmajor(x)
+    else:
+        n = int(np.asarray(y).shape[0])
+    y_idx = np.searchsorted(clf.classes_, np.asarray(y, dtype=np.float64)).astype(np.uint8)
+    dev = x.device
+    y_dev = torch.from_numpy(y_idx).to(dev)
+    rs = random_state if isinstance(random_state, np.random.RandomState) else np.random.RandomState(random_state)
+    random_seed = rs.randint(np.iinfo(np.int32).max + 1)         # SK/inspection/_permutation_importance.py:278
+    perms = torch.from_numpy(shuffled_indices(n, n_repeats, random_seed)).to(dev)
+    n_feat = clf.n_features_in_
+    counts = torch.zeros(1 + n_feat * n_repeats, dtype=torch.int64, device=dev)
+    status = clf.new_status()
+    jobs = [(-1, 0)] + [(c, r) for c in range(n_feat) for r in range(n_repeats)]
+    for k, (col, rep) in enumerate(jobs):
+        if k % world != rank:
+            continue
+        clf.score_device(x, n=n, perm_col=col, perm_idx=perms[rep] if col >= 0 else None, y=y_dev,
+                         score=counts[k:k + 1], status=status)
+    if world > 1:
+        torch.distributed.all_reduce(counts)
+    acc = counts.cpu().numpy().astype(np.float64) / n
+    baseline = acc[0]
+    scores = acc[1:].reshape(n_feat, n_repeats)
+    importances = baseline - scores
+    return ImportanceResult(importances_mean=importances.mean(axis=1), importances_std=importances.std(axis=1),
+                            importances=importances, baseline_score=baseline)

@@ -5,8 +5,8 @@
 * ``without_member`` -- the same stack minus one member kind (e.g. the SVC-free stack, the part of the ensemble that is
   genuinely HBM-bound: SURVEY.md section 8d).
 
-Trees are built as plain ``TreeTable`` arrays (what ``Tree.__getstate__`` holds); the oracle scores them through
-``Tree.__setstate__`` (oracle/sk_rebuild.py), the GPU through the same blob as any other model.
+Trees are built as plain ``TreeTable`` arrays (what ``Tree.__getstate__`` holds); the tests hand the same arrays to
+scikit-learn through ``Tree.__setstate__``, the GPU gets them through the same blob as any other model.
 """
 from __future__ import annotations
 

@@ -40,4 +40,5 @@ def test_product_does_not_import_the_oracle():
         for f in files:
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 src = open(os.path.join(base, f)).read()
-                assert "oracle" not in src.replace("oracle/", ""), f"{f} mentions the oracle package"
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), f"{f} imports the oracle"
+                assert "stack_oracle" not in src and "sk_rebuild" not in src, f"{f} reaches into the oracle package"

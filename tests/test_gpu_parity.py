@@ -298,3 +298,22 @@ def test_live_sklearn_object_drop_in(pkg, torch_cuda):
         assert np.array_equal(fast.predict(Xs), clf.predict(Xs))
         gi = 1
         assert np.array_equal(fast.apply(Xs), clf.estimators_[gi].apply(Xs)[:, :, 0].astype(np.int64))
+
+
+def test_permutation_importance_matches_sklearn(pkg, published, clf_for, torch_cuda):
+    """BASELINE config 5 at a size scikit-learn finishes in seconds: same seeds -> same shuffles -> same importances."""
+    from sklearn.inspection import permutation_importance as sk_pi
+
+    from oracle import sk_rebuild
+
+    n = 3000
+    X = pkg.synth.host_rows(published["specs"], 8, 0, n).astype(np.float64)
+    rng = np.random.default_rng(3)
+    y = (so.predict_proba(published["arrays"], X)[:, 1] > rng.random(n)).astype(np.float64)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        ref = sk_pi(sk_rebuild.rebuild_stack(published["arrays"]), X, y, n_repeats=3, random_state=7)
+    got = pkg.inspection.permutation_importance(clf_for(published), X, y, n_repeats=3, random_state=7)
+    assert np.array_equal(got.importances.shape, ref.importances.shape)
+    assert np.abs(got.importances - ref.importances).max() < 1e-12        # accuracies are integer counts / n
+    assert np.abs(got.importances_mean - ref.importances_mean).max() < 1e-12
