@@ -29,6 +29,9 @@ constexpr int TREE_CHUNK = 16;            // float32 partial sums over trees are
 #ifndef HFE_PERSISTENT
 #define HFE_PERSISTENT 0                  // 1: resident blocks loop over tiles; 0: one 128-row tile per warp (measured faster)
 #endif
+#ifndef HFE_MIN_BLOCKS_NOSVC
+#define HFE_MIN_BLOCKS_NOSVC 8            // without the RBF loop the kernel is a streaming pass: trade registers for warps
+#endif
 #ifndef HFE_MIN_BLOCKS
 #define HFE_MIN_BLOCKS 4                  // resident blocks per SM the fused kernel is compiled for (128-register cap)
 #endif
@@ -326,7 +329,7 @@ constexpr int WARP_ROWS = 32 * ROWS_PER_THREAD;          // rows one warp scores
 constexpr int BLOCK_WARPS = BLOCK_THREADS / 32;
 
 template <bool SVC, int TREE_MODE>
-__global__ void __launch_bounds__(BLOCK_THREADS, HFE_MIN_BLOCKS)
+__global__ void __launch_bounds__(BLOCK_THREADS, SVC ? HFE_MIN_BLOCKS : HFE_MIN_BLOCKS_NOSVC)
 hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float4* s_sv = reinterpret_cast<float4*>(smem_raw);                       // [smem_groups][SV_STEPS] (+pad)
@@ -355,9 +358,52 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
     const bool has_lin = P.slot_lin >= 0;
     constexpr int R = ROWS_PER_THREAD;
 
+    const bool full = (row0 + R <= P.n);
+    double raw[R], zl[R];
+    float zz32[R];
+    float2 z2[F][R / 2];
+    bool nonfinite;
+#pragma unroll
+    for (int r = 0; r < R; ++r) { raw[r] = 0.0; zl[r] = P.lin_intercept; zz32[r] = 0.f; }
+    if (!SVC) {
+        // ---- streaming prologue for stacks without the SVC member (the HBM-bound configuration): one feature column at
+        //      a time -- load, finiteness probe, logistic dot product, that feature's stump splits -- so only a few
+        //      registers are live and twice as many warps fit on an SM to keep loads in flight ------------------------
+        float finite_probe = 0.f, acc[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) acc[r] = 0.f;
+#pragma unroll
+        for (int f = 0; f < F; ++f) {
+            float xf[R];
+            if (full && f != P.perm_col) {
+                float4 v = __ldg(reinterpret_cast<const float4*>(P.x + (long long)f * P.ld + row0));
+                xf[0] = v.x; xf[1] = v.y; xf[2] = v.z; xf[3] = v.w;
+            } else {
+#pragma unroll
+                for (int r = 0; r < R; ++r) xf[r] = (row0 + r < P.n) ? load_feature(P, f, row0 + r) : 0.0f;
+            }
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                finite_probe = fmaf(xf[r], 0.f, finite_probe);
+                if (has_lin) zl[r] = fma((double)xf[r], P.lin_coef[f], zl[r]);
+                if (TREE_MODE == 2) s_xt[f * BLOCK_ROWS + r * BLOCK_THREADS + tid] = xf[r];
+            }
+            if (TREE_MODE == 1) {
+                for (int s = P.split_begin[f]; s < P.split_begin[f + 1]; ++s) {
+                    float thr = P.split_thr[s], dl = P.split_delta[s];
+#pragma unroll
+                    for (int r = 0; r < R; ++r) acc[r] += (xf[r] <= thr) ? dl : 0.f;
+                }
+            }
+        }
+        nonfinite = !(finite_probe == 0.f);
+        if (TREE_MODE == 1) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) raw[r] = P.gbt_split_base + (double)acc[r];
+        }
+    } else {
     // ---- load 4 rows x 17 features (128-bit loads; guarded scalar loads on the ragged tail / permuted column) ------
     float xv[F][R];
-    const bool full = (row0 + R <= P.n);
 #pragma unroll
     for (int f = 0; f < F; ++f) {
         if (full && f != P.perm_col) {
@@ -373,7 +419,7 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
     for (int f = 0; f < F; ++f)
 #pragma unroll
         for (int r = 0; r < R; ++r) finite_probe = fmaf(xv[f][r], 0.f, finite_probe);
-    const bool nonfinite = !(finite_probe == 0.f);
+    nonfinite = !(finite_probe == 0.f);
 
     if (TREE_MODE == 2) {
 #pragma unroll
@@ -383,9 +429,6 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
     }
 
     // ---- boosted trees ---------------------------------------------------------------------------------------------
-    double raw[R];
-#pragma unroll
-    for (int r = 0; r < R; ++r) raw[r] = 0.0;
     if (TREE_MODE == 1) {
         float acc[R];
 #pragma unroll
@@ -400,7 +443,29 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
         }
 #pragma unroll
         for (int r = 0; r < R; ++r) raw[r] = P.gbt_split_base + (double)acc[r];
-    } else if (TREE_MODE == 2) {
+    }
+
+    // ---- logistic member (float64) and standardisation (float32, mean split hi+lo so x - mean stays exact-ish) -------
+    // z2[f][p] packs rows (2p, 2p+1) of feature f into one 64-bit register pair for FFMA2.
+#pragma unroll
+    for (int f = 0; f < F; ++f) {
+        float zf[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            if (has_lin) zl[r] = fma((double)xv[f][r], P.lin_coef[f], zl[r]);
+            zf[r] = 0.f;
+            if (SVC) {
+                zf[r] = ((xv[f][r] - P.mean_hi[f]) - P.mean_lo[f]) * P.inv_scale32[f];
+                zz32[r] = fmaf(zf[r], zf[r], zz32[r]);
+            }
+        }
+#pragma unroll
+        for (int p = 0; p < R / 2; ++p) z2[f][p] = make_float2(zf[2 * p], zf[2 * p + 1]);
+    }
+    }   // full prologue
+
+    // ---- general boosted trees: predicated fixed-depth walk, x from this thread's shared-memory slots ----------------
+    if (TREE_MODE == 2) {
         // own rows only: no barrier needed between the s_xt stores above and these loads
 #pragma unroll
         for (int r = 0; r < R; ++r) raw[r] = P.gbt_init;
@@ -431,28 +496,7 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
         }
     }
 
-    // ---- logistic member (float64) and standardisation (float32, mean split hi+lo so x - mean stays exact-ish) -------
-    // z2[f][p] packs rows (2p, 2p+1) of feature f into one 64-bit register pair for FFMA2.
-    double zl[R];
-    float zz32[R];
-#pragma unroll
-    for (int r = 0; r < R; ++r) { zl[r] = P.lin_intercept; zz32[r] = 0.f; }
-    float2 z2[F][R / 2];
-#pragma unroll
-    for (int f = 0; f < F; ++f) {
-        float zf[R];
-#pragma unroll
-        for (int r = 0; r < R; ++r) {
-            if (has_lin) zl[r] = fma((double)xv[f][r], P.lin_coef[f], zl[r]);
-            zf[r] = 0.f;
-            if (SVC) {
-                zf[r] = ((xv[f][r] - P.mean_hi[f]) - P.mean_lo[f]) * P.inv_scale32[f];
-                zz32[r] = fmaf(zf[r], zf[r], zz32[r]);
-            }
-        }
-#pragma unroll
-        for (int p = 0; p < R / 2; ++p) z2[f][p] = make_float2(zf[2 * p], zf[2 * p + 1]);
-    }
+
     // Links of the tree and logistic members now, so that only their share of the combiner's logit (one double per
     // row) has to stay in registers across the RBF loop.
     double zpart[R], member[3][R];

@@ -12,8 +12,14 @@ import mlr_b200 as P  # noqa: E402
 name = os.environ.get("NCU_MODEL", "published")
 n = int(os.environ.get("NCU_ROWS", 4_000_000))
 gold = os.path.join(ROOT, "tests", "golden")
-clf = P.HFStackB200.from_blob_file(os.path.join(gold, f"{name}_model.blob"))
-if name == "published":
+base = "retrained" if name == "retrained" else "published"
+arrays = P.export.read_blob(open(os.path.join(gold, f"{base}_model.blob"), "rb").read())
+if name == "nosvc":
+    arrays = P.synth_models.without_member(arrays, "svc")
+elif name == "stress":
+    arrays = P.synth_models.stress_stack(arrays, with_svc=False)
+clf = P.HFStackB200.from_arrays(arrays)
+if base == "published":
     specs = P.synth.schema_specs()
 else:
     cand = P.synth.candidate_specs()
