@@ -343,10 +343,24 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
     // every warp scores its own 128-row tile(s) with no further block-level synchronisation.  With HFE_PERSISTENT the
     // grid is sized to the resident block count and warps loop over tiles; measured on B200 the plain one-tile-per-warp
     // grid is ~15 % faster (the hardware block scheduler staggers blocks better than a static tile assignment).
+    // TMA bulk copy (cp.async.bulk, SASS UBLKCP): one thread asks the copy engine for the whole table (plus its zero
+    // pad) and every thread goes straight on to load and standardise its rows; the mbarrier is only waited on right
+    // before the RBF loop, by which time the bytes have normally landed.
+    __shared__ __align__(8) unsigned long long s_table_ready;
     if (SVC) {
-        for (int i = tid; i < P.n_groups * SV_STEPS + SV_PAD_ROWS; i += BLOCK_THREADS)
-            s_sv[i] = (i < P.n_groups * SV_STEPS) ? __ldg(P.sv_tab + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        const unsigned mbar = (unsigned)__cvta_generic_to_shared(&s_table_ready);
+        if (tid == 0) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mbar));
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
         __syncthreads();
+        if (tid == 0) {
+            const unsigned bytes = (unsigned)((P.n_groups * SV_STEPS + SV_PAD_ROWS) * sizeof(float4));
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(bytes) : "memory");
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         ::"r"((unsigned)__cvta_generic_to_shared(s_sv)), "l"(P.sv_tab), "r"(bytes), "r"(mbar)
+                         : "memory");
+        }
     }
 #if HFE_PERSISTENT
     for (int tile = blockIdx.x * BLOCK_WARPS + (tid >> 5); tile < n_tiles; tile += gridDim.x * BLOCK_WARPS) {
@@ -521,6 +535,18 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
 #pragma unroll
     for (int r = 0; r < R; ++r) acc64[r] = 0.0;
     if (SVC) {
+        {
+            const unsigned mbar = (unsigned)__cvta_generic_to_shared(&s_table_ready);
+            asm volatile(
+                "{\n"
+                ".reg .pred p;\n"
+                "TABLE_WAIT_%=:\n"
+                "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], 0;\n"
+                "@p bra TABLE_DONE_%=;\n"
+                "bra TABLE_WAIT_%=;\n"
+                "TABLE_DONE_%=:\n"
+                "}\n" ::"r"(mbar) : "memory");
+        }
         {
             const int ng = P.n_groups;
             const float4* tab = s_sv;
