@@ -54,7 +54,7 @@ int launch_score(const Model* m, const ScoreParams& P, cudaStream_t stream) {
     // persistent blocks: every warp walks its own sequence of 128-row tiles
     long long tiles = (P.n + WARP_ROWS - 1) / WARP_ROWS;
     long long blocks = (tiles + BLOCK_WARPS - 1) / BLOCK_WARPS;
-    if (HFE_PERSISTENT) blocks = std::min<long long>(blocks, (long long)sms * per_sm);
+    if (HFE_PERSISTENT || !SVC) blocks = std::min<long long>(blocks, (long long)sms * per_sm);
     kernel<<<(unsigned)blocks, BLOCK_THREADS, smem, stream>>>(P, P.n_groups);
     HFE_CUDA_TRY(cudaGetLastError());
     return HFE_OK;

@@ -240,6 +240,17 @@ __device__ __forceinline__ float load_feature(const ScoreParams& P, int f, long 
     return __ldg(P.x + (long long)f * P.ld + src);
 }
 
+// Ragged tail / permuted column: up to four guarded scalar loads.  Out of line (it is rare, and inlining it 17 times per
+// prologue makes the kernel's code footprint several times larger than its hot loop).
+__device__ __noinline__ float4 load_rows_slow(const ScoreParams& P, int f, long long row0) {
+    float4 v;
+    v.x = (row0 + 0 < P.n) ? load_feature(P, f, row0 + 0) : 0.0f;
+    v.y = (row0 + 1 < P.n) ? load_feature(P, f, row0 + 1) : 0.0f;
+    v.z = (row0 + 2 < P.n) ? load_feature(P, f, row0 + 2) : 0.0f;
+    v.w = (row0 + 3 < P.n) ? load_feature(P, f, row0 + 3) : 0.0f;
+    return v;
+}
+
 // Walk one tree for one row: x values come from `xrow` (F floats, any address space).  Returns the re-laid leaf index
 // (global node index).
 template <typename XGet>
@@ -362,12 +373,11 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
                          : "memory");
         }
     }
-#if HFE_PERSISTENT
-    for (int tile = blockIdx.x * BLOCK_WARPS + (tid >> 5); tile < n_tiles; tile += gridDim.x * BLOCK_WARPS) {
-#else
-    const int tile = blockIdx.x * BLOCK_WARPS + (tid >> 5);
-    if (tile < n_tiles) {
-#endif
+    // SVC-free instances are short streaming passes: resident blocks loop over tiles (grid-stride) so the code stays
+    // warm in the instruction cache.  With the RBF loop the one-tile-per-warp grid measured ~15 % faster.
+    constexpr bool kPersistent = HFE_PERSISTENT || !SVC;
+    for (int tile = blockIdx.x * BLOCK_WARPS + (tid >> 5); tile < n_tiles;
+         tile += kPersistent ? gridDim.x * BLOCK_WARPS : n_tiles) {
     const long long row0 = (long long)tile * WARP_ROWS + lane * ROWS_PER_THREAD;
     const bool has_lin = P.slot_lin >= 0;
     constexpr int R = ROWS_PER_THREAD;
@@ -393,8 +403,8 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
                 float4 v = __ldg(reinterpret_cast<const float4*>(P.x + (long long)f * P.ld + row0));
                 xf[0] = v.x; xf[1] = v.y; xf[2] = v.z; xf[3] = v.w;
             } else {
-#pragma unroll
-                for (int r = 0; r < R; ++r) xf[r] = (row0 + r < P.n) ? load_feature(P, f, row0 + r) : 0.0f;
+                float4 v = load_rows_slow(P, f, row0);
+                xf[0] = v.x; xf[1] = v.y; xf[2] = v.z; xf[3] = v.w;
             }
 #pragma unroll
             for (int r = 0; r < R; ++r) {
@@ -403,7 +413,9 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
                 if (TREE_MODE == 2) s_xt[f * BLOCK_ROWS + r * BLOCK_THREADS + tid] = xf[r];
             }
             if (TREE_MODE == 1) {
-                for (int s = P.split_begin[f]; s < P.split_begin[f + 1]; ++s) {
+#pragma unroll 1
+    #pragma unroll 1
+            for (int s = P.split_begin[f]; s < P.split_begin[f + 1]; ++s) {
                     float thr = P.split_thr[s], dl = P.split_delta[s];
 #pragma unroll
                     for (int r = 0; r < R; ++r) acc[r] += (xf[r] <= thr) ? dl : 0.f;
@@ -424,8 +436,8 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
             float4 v = __ldg(reinterpret_cast<const float4*>(P.x + (long long)f * P.ld + row0));
             xv[f][0] = v.x; xv[f][1] = v.y; xv[f][2] = v.z; xv[f][3] = v.w;
         } else {
-#pragma unroll
-            for (int r = 0; r < R; ++r) xv[f][r] = (row0 + r < P.n) ? load_feature(P, f, row0 + r) : 0.0f;
+            float4 v = load_rows_slow(P, f, row0);
+            xv[f][0] = v.x; xv[f][1] = v.y; xv[f][2] = v.z; xv[f][3] = v.w;
         }
     }
     float finite_probe = 0.f;                       // x * 0 is NaN exactly when x is NaN or +-Inf
@@ -449,6 +461,7 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
         for (int r = 0; r < R; ++r) acc[r] = 0.f;
 #pragma unroll
         for (int f = 0; f < F; ++f) {
+#pragma unroll 1
             for (int s = P.split_begin[f]; s < P.split_begin[f + 1]; ++s) {
                 float thr = P.split_thr[s], dl = P.split_delta[s];
 #pragma unroll
