@@ -25,6 +25,7 @@ constexpr int BLOCK_THREADS = HFE_BLOCK_THREADS;
 constexpr int ROWS_PER_THREAD = 4;
 constexpr int BLOCK_ROWS = BLOCK_THREADS * ROWS_PER_THREAD;
 constexpr int MAX_SMEM_GROUPS = 384;      // support-vector groups staged per pass (384*18*16 B = 108 KB; 2 blocks/SM)
+constexpr int STREAM_WINDOW = 6;          // feature columns in flight per thread in the SVC-free streaming prologue
 constexpr int TREE_CHUNK = 16;            // float32 partial sums over trees are folded into float64 every 16 trees
 #ifndef HFE_PERSISTENT
 #define HFE_PERSISTENT 0                  // 1: resident blocks loop over tiles; 0: one 128-row tile per warp (measured faster)
@@ -240,14 +241,28 @@ __device__ __forceinline__ float load_feature(const ScoreParams& P, int f, long 
     return __ldg(P.x + (long long)f * P.ld + src);
 }
 
-// Ragged tail / permuted column: up to four guarded scalar loads.  Out of line (it is rare, and inlining it 17 times per
-// prologue makes the kernel's code footprint several times larger than its hot loop).
-__device__ __noinline__ float4 load_rows_slow(const ScoreParams& P, int f, long long row0) {
-    float4 v;
-    v.x = (row0 + 0 < P.n) ? load_feature(P, f, row0 + 0) : 0.0f;
-    v.y = (row0 + 1 < P.n) ? load_feature(P, f, row0 + 1) : 0.0f;
-    v.z = (row0 + 2 < P.n) ? load_feature(P, f, row0 + 2) : 0.0f;
-    v.w = (row0 + 3 < P.n) ? load_feature(P, f, row0 + 3) : 0.0f;
+// Four consecutive rows of one feature column.  The 128-bit load is always in bounds: row0 is a multiple of 4 below n
+// and ld is a multiple of 4 not below n.  It is kept free of control flow so that a thread's 17 column loads can all
+// be in flight at once; fix_rows4 patches the rare cases afterwards.
+__device__ __forceinline__ float4 load_rows4(const ScoreParams& P, int f, long long row0) {
+    return __ldg(reinterpret_cast<const float4*>(P.x + (long long)f * P.ld + row0));
+}
+
+// Rows at or beyond n (ragged last tile) read padding and are zeroed; a permuted column is gathered through perm_idx.
+__device__ __forceinline__ float4 fix_rows4(const ScoreParams& P, int f, long long row0, bool full, float4 v) {
+    if (f == P.perm_col) {
+        const float* col = P.x + (long long)f * P.ld;
+        const int* idx = P.perm_idx + row0;
+        v.x = __ldg(col + __ldg(idx));
+        if (full || row0 + 1 < P.n) v.y = __ldg(col + __ldg(idx + 1));
+        if (full || row0 + 2 < P.n) v.z = __ldg(col + __ldg(idx + 2));
+        if (full || row0 + 3 < P.n) v.w = __ldg(col + __ldg(idx + 3));
+    }
+    if (!full) {
+        if (row0 + 1 >= P.n) v.y = 0.f;
+        if (row0 + 2 >= P.n) v.z = 0.f;
+        if (row0 + 3 >= P.n) v.w = 0.f;
+    }
     return v;
 }
 
@@ -396,16 +411,20 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
         float finite_probe = 0.f, acc[R];
 #pragma unroll
         for (int r = 0; r < R; ++r) acc[r] = 0.f;
+        // a window of STREAM_WINDOW feature columns is kept in flight: column f+W is requested before column f is used
+        constexpr int W = STREAM_WINDOW;
+        auto load_col = [&](int f) -> float4 { return load_rows4(P, f, row0); };
+        const bool needs_fix = !full || P.perm_col >= 0;
+        float4 win[W];
+#pragma unroll
+        for (int i = 0; i < W; ++i) win[i] = load_col(i);
 #pragma unroll
         for (int f = 0; f < F; ++f) {
+            float4 v = win[f % W];
+            if (f + W < F) win[f % W] = load_col(f + W);
+            if (needs_fix) v = fix_rows4(P, f, row0, full, v);
             float xf[R];
-            if (full && f != P.perm_col) {
-                float4 v = __ldg(reinterpret_cast<const float4*>(P.x + (long long)f * P.ld + row0));
-                xf[0] = v.x; xf[1] = v.y; xf[2] = v.z; xf[3] = v.w;
-            } else {
-                float4 v = load_rows_slow(P, f, row0);
-                xf[0] = v.x; xf[1] = v.y; xf[2] = v.z; xf[3] = v.w;
-            }
+            xf[0] = v.x; xf[1] = v.y; xf[2] = v.z; xf[3] = v.w;
 #pragma unroll
             for (int r = 0; r < R; ++r) {
                 finite_probe = fmaf(xf[r], 0.f, finite_probe);
@@ -432,11 +451,13 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
     float xv[F][R];
 #pragma unroll
     for (int f = 0; f < F; ++f) {
-        if (full && f != P.perm_col) {
-            float4 v = __ldg(reinterpret_cast<const float4*>(P.x + (long long)f * P.ld + row0));
-            xv[f][0] = v.x; xv[f][1] = v.y; xv[f][2] = v.z; xv[f][3] = v.w;
-        } else {
-            float4 v = load_rows_slow(P, f, row0);
+        float4 v = load_rows4(P, f, row0);
+        xv[f][0] = v.x; xv[f][1] = v.y; xv[f][2] = v.z; xv[f][3] = v.w;
+    }
+    if (!full || P.perm_col >= 0) {              // rare: ragged last tile, or a permutation-importance pass
+#pragma unroll
+        for (int f = 0; f < F; ++f) {
+            float4 v = fix_rows4(P, f, row0, full, make_float4(xv[f][0], xv[f][1], xv[f][2], xv[f][3]));
             xv[f][0] = v.x; xv[f][1] = v.y; xv[f][2] = v.z; xv[f][3] = v.w;
         }
     }
