@@ -403,7 +403,7 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
     const bool full = (row0 + R <= P.n);
     double raw[R], zl[R];
     float zz32[R];
-    float2 z2[F][R / 2];
+    float zs[F][R];                 // standardised features, one scalar register per (feature, row)
     bool nonfinite;
 #pragma unroll
     for (int r = 0; r < R; ++r) { raw[r] = 0.0; zl[r] = P.lin_intercept; zz32[r] = 0.f; }
@@ -502,21 +502,17 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
     }
 
     // ---- logistic member (float64) and standardisation (float32, mean split hi+lo so x - mean stays exact-ish) -------
-    // z2[f][p] packs rows (2p, 2p+1) of feature f into one 64-bit register pair for FFMA2.
 #pragma unroll
     for (int f = 0; f < F; ++f) {
-        float zf[R];
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             if (has_lin) zl[r] = fma((double)xv[f][r], P.lin_coef[f], zl[r]);
-            zf[r] = 0.f;
+            zs[f][r] = 0.f;
             if (SVC) {
-                zf[r] = ((xv[f][r] - P.mean_hi[f]) - P.mean_lo[f]) * P.inv_scale32[f];
-                zz32[r] = fmaf(zf[r], zf[r], zz32[r]);
+                zs[f][r] = ((xv[f][r] - P.mean_hi[f]) - P.mean_lo[f]) * P.inv_scale32[f];
+                zz32[r] = fmaf(zs[f][r], zs[f][r], zz32[r]);
             }
         }
-#pragma unroll
-        for (int p = 0; p < R / 2; ++p) z2[f][p] = make_float2(zf[2 * p], zf[2 * p + 1]);
     }
     }   // full prologue
 
@@ -566,13 +562,14 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
         }
     }
 
-    // ---- RBF sum: 4 support vectors x 4 rows per tile, packed FFMA2 ------------------------------------------------------
+    // ---- RBF sum: 4 support vectors x R rows per tile, packed FFMA2 ------------------------------------------------------
     // Each table step is one float4 = the weights of 4 support vectors for one feature (step F: their folded
-    // coefficients).  A weight enters FFMA2 as a broadcast scalar operand (SASS ``Rw.F32``); the two 64-bit operands
-    // are a pair of rows of z and the pair's running exponents.  The table streams from shared memory through a
-    // 3-deep register ring (LDS.128 issued two steps ahead of first use).  The 16 exp2 (MUFU) + 8 coefficient FFMA2s
-    // of group g-1 are interleaved with the FFMA2s of group g so every warp uses the XU and FMA pipes evenly instead
-    // of in bursts (warps of a block run in lockstep).
+    // coefficients).  An FFMA2 covers two support vectors: its 64-bit operands are a weight pair (.xy or .zw of the
+    // LDS.128 result) and the pair's running exponents, the row's standardised feature enters as a broadcast scalar
+    // (SASS ``Rz.F32``).  The four rows that share a weight pair are issued back to back, and the second pair walks
+    // the rows in reverse, so consecutive FFMA2s always share one source operand (register-file reuse cache) --
+    // measured +4 points of FMA-pipe utilisation over the row-paired form (tools/microbench3.cu).
+    // The table streams from shared memory through a 3-deep register ring (LDS.128 two steps ahead of first use).
     double acc64[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) acc64[r] = 0.0;
@@ -589,46 +586,46 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
                 "TABLE_DONE_%=:\n"
                 "}\n" ::"r"(mbar) : "memory");
         }
-        {
-            const int ng = P.n_groups;
-            const float4* tab = s_sv;
-            float4 ring[3];
-            ring[0] = tab[0]; ring[1] = tab[1];
+        const float4* tab = s_sv;
+        float4 ring[3];
+        ring[0] = tab[0]; ring[1] = tab[1];
 #pragma unroll 1
-            for (int g = 0; g < ng; ++g) {
-                float2 t2[SV_GROUP][R / 2];
+        for (int g = 0; g < P.n_groups; ++g) {
+            float2 t2[SV_GROUP / 2][R];                   // [support-vector pair][row]
 #pragma unroll
-                for (int st = 0; st < SV_STEPS; ++st) {
-                    ring[(st + 2) % 3] = tab[st + 2];
-                    const float4 w4 = ring[st % 3];
-                    const float w[SV_GROUP] = {w4.x, w4.y, w4.z, w4.w};
-                    if (st == 0) {
+            for (int st = 0; st < SV_STEPS; ++st) {
+                ring[(st + 2) % 3] = tab[st + 2];         // SV_STEPS % 3 == 0: same ring slot in every group
+                const float4 w4 = ring[st % 3];
+                const float2 wp[SV_GROUP / 2] = {make_float2(w4.x, w4.y), make_float2(w4.z, w4.w)};
+                if (st == 0) {
 #pragma unroll
-                        for (int p = 0; p < R / 2; ++p)
+                    for (int h = 0; h < SV_GROUP / 2; ++h)
 #pragma unroll
-                            for (int q = 0; q < SV_GROUP; ++q) t2[q][p] = __fmul2_rn(z2[0][p], make_float2(w[q], w[q]));
-                    } else if (st < F) {
+                        for (int r = 0; r < R; ++r) t2[h][r] = __fmul2_rn(wp[h], make_float2(zs[0][r], zs[0][r]));
+                } else if (st < F) {
 #pragma unroll
-                        for (int p = 0; p < R / 2; ++p)
+                    for (int h = 0; h < SV_GROUP / 2; ++h)
 #pragma unroll
-                            for (int q = 0; q < SV_GROUP; ++q)
-                                t2[q][p] = __ffma2_rn(z2[st][p], make_float2(w[q], w[q]), t2[q][p]);
-                    } else {
-#pragma unroll
-                        for (int p = 0; p < R / 2; ++p) {
-                            float2 a2 = make_float2(0.f, 0.f);
-#pragma unroll
-                            for (int q = 0; q < SV_GROUP; ++q) {
-                                float2 e = make_float2(ex2_approx(t2[q][p].x), ex2_approx(t2[q][p].y));
-                                a2 = __ffma2_rn(e, make_float2(w[q], w[q]), a2);
-                            }
-                            acc64[2 * p] += (double)a2.x;
-                            acc64[2 * p + 1] += (double)a2.y;
+                        for (int rr = 0; rr < R; ++rr) {
+                            const int r = (h & 1) ? R - 1 - rr : rr;
+                            t2[h][r] = __ffma2_rn(wp[h], make_float2(zs[st][r], zs[st][r]), t2[h][r]);
                         }
+                } else {
+                    // exp2 of the 4 x R exponents, weighted by the folded coefficients (wp holds them in this step);
+                    // the float32 partial sum of these 4 vectors goes straight into the float64 accumulator
+#pragma unroll
+                    for (int r = 0; r < R; ++r) {
+                        float2 a2 = make_float2(0.f, 0.f);
+#pragma unroll
+                        for (int h = 0; h < SV_GROUP / 2; ++h) {
+                            float2 e = make_float2(ex2_approx(t2[h][r].x), ex2_approx(t2[h][r].y));
+                            a2 = __ffma2_rn(e, wp[h], a2);
+                        }
+                        acc64[r] += (double)(a2.x + a2.y);
                     }
                 }
-                tab += SV_STEPS;
             }
+            tab += SV_STEPS;
         }
     }
 
