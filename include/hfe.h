@@ -126,6 +126,14 @@ int hfe_ingest_rowmajor_f64(const double* x_rowmajor, int64_t n, int32_t n_featu
 int hfe_ingest_rowmajor_f32(const float* x_rowmajor, int64_t n, int32_t n_features, float* x, int64_t ld,
                             uint32_t* status, void* stream);
 
+/* The evaluation train_ensemble_public.py:63-64,67,79 performs next on the probabilities (classification_report of
+ * ``y_pred[:,1] > 0.5``, ROC and precision-recall curves): confusion[0..3] = tn, fp, fn, tp at `threshold` (uint64,
+ * zeroed by the call); hist (may be NULL) = 2 x HFE_METRIC_BINS uint32, per true class the histogram of P(class 1) in
+ * bins floor(p*(BINS-1)+0.5), from which the curves and their areas follow on the host. */
+#define HFE_METRIC_BINS 65536
+int hfe_binary_metrics(const float* proba_n2, const uint8_t* y, int64_t n, float threshold,
+                       unsigned long long* confusion, uint32_t* hist, void* stream);
+
 /* Host-buffer convenience used by the facade for numpy inputs: copies X (row-major float64, host) to the device,
  * ingests, scores, copies P back (float64 [n,2]; p0 = 1 - p1) and synchronises.  Allocates temporaries.
  * labels / decision / meta may be NULL.  Returns HFE_ERR_NONFINITE_INPUT when X holds NaN/Inf. */

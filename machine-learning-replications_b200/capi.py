@@ -16,11 +16,12 @@ STATUS_WORDS = STATUS_HEADER_WORDS + WORKLIST_CAPACITY      # 65536 uint32 = 256
 ROW_NONFINITE = 1
 WORKLIST_OVERFLOW = 2
 NOALLOC_MAX_ROWS = 1 << 26
+METRIC_BINS = 65536
 
 EXPORTS = [
     "hfe_abi_version", "hfe_last_error_string", "hfe_model_create", "hfe_model_destroy", "hfe_model_get_info",
     "hfe_predict_proba", "hfe_predict", "hfe_score", "hfe_apply", "hfe_predict_proba_f64", "hfe_synth_rows",
-    "hfe_ingest_rowmajor_f64", "hfe_ingest_rowmajor_f32", "hfe_predict_host", "hfe_predict_proba_noalloc",
+    "hfe_ingest_rowmajor_f64", "hfe_ingest_rowmajor_f32", "hfe_predict_host", "hfe_predict_proba_noalloc", "hfe_binary_metrics",
 ]
 
 
@@ -69,6 +70,7 @@ def load_library(path: str = LIB_PATH):
     lib.hfe_ingest_rowmajor_f32.argtypes = [vp, i64, i32, vp, i64, vp, vp]
     lib.hfe_predict_host.argtypes = [vp, vp, i64, vp, vp, vp, vp]
     lib.hfe_predict_proba_noalloc.argtypes = [vp, vp, i64, i64, vp, vp, vp]
+    lib.hfe_binary_metrics.argtypes = [vp, vp, i64, C.c_float, vp, vp, vp]
     for name in EXPORTS:
         fn = getattr(lib, name)
         if name not in ("hfe_last_error_string", "hfe_model_destroy"):

@@ -257,6 +257,20 @@ int hfe_ingest_rowmajor_f32(const float* x_rowmajor, int64_t n, int32_t n_featur
     return ingest_common(x_rowmajor, n, n_features, x, ld, status, stream);
 }
 
+int hfe_binary_metrics(const float* proba_n2, const uint8_t* y, int64_t n, float threshold,
+                       unsigned long long* confusion, uint32_t* hist, void* stream) {
+    if (n < 0 || !confusion) return fail(HFE_ERR_INVALID_ARGUMENT, "bad metrics arguments");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    HFE_CUDA_TRY(cudaMemsetAsync(confusion, 0, 4 * sizeof(unsigned long long), s));
+    if (hist) HFE_CUDA_TRY(cudaMemsetAsync(hist, 0, 2 * METRIC_BINS * sizeof(uint32_t), s));
+    if (n == 0) return HFE_OK;
+    if (!proba_n2 || !y) return fail(HFE_ERR_INVALID_ARGUMENT, "null metrics input");
+    long long blocks = std::min<long long>((n + 255) / 256, 148LL * 8);
+    hfe_metrics_kernel<<<(unsigned)blocks, 256, 0, s>>>(proba_n2, y, n, threshold, confusion, hist);
+    HFE_CUDA_TRY(cudaGetLastError());
+    return HFE_OK;
+}
+
 // ---- allocation-free variant ------------------------------------------------------------------------------------------
 // Scratch for hfe_predict_proba_noalloc: the status header + work list that the fused kernel and the fix-up kernel
 // share, kept in the library image (256 KiB of device memory per GPU that loads this library) so that the call never

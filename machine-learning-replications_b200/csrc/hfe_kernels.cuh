@@ -787,4 +787,33 @@ hfe_ingest_kernel(const T* __restrict__ src, long long n, int nf, float* __restr
     if (bad) atomicOr(status, HFE_ROW_NONFINITE);
 }
 
+// ---- evaluation counts (what train_ensemble_public.py:63-64,67,79 computes next from the probabilities) ---------------------
+// confusion[0..3] = tn, fp, fn, tp at `threshold` (the script's ``y_pred[:,1] > 0.5``); hist[c*NB + b] counts rows of true
+// class c whose P(class 1) falls in bin b = floor(p * (NB-1) + 0.5): ROC / precision-recall curves and their areas follow
+// from the two histograms on the host.
+constexpr int METRIC_BINS = 65536;
+
+__global__ void __launch_bounds__(256)
+hfe_metrics_kernel(const float* __restrict__ proba, const unsigned char* __restrict__ y, long long n, float threshold,
+                   unsigned long long* confusion, unsigned int* hist) {
+    unsigned cnt[4] = {0, 0, 0, 0};
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        float p = __ldg(proba + 2 * i + 1);
+        int c = y[i] ? 1 : 0;
+        int pred = p > threshold ? 1 : 0;
+        cnt[c * 2 + pred] += 1;
+        if (hist) {
+            int b = (int)fminf(fmaxf(p * (float)(METRIC_BINS - 1) + 0.5f, 0.f), (float)(METRIC_BINS - 1));
+            atomicAdd(hist + c * METRIC_BINS + b, 1u);
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        unsigned v = cnt[k];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xFFFFFFFFu, v, o);
+        if ((threadIdx.x & 31) == 0 && v) atomicAdd(confusion + k, (unsigned long long)v);
+    }
+}
+
 }  // namespace hfe

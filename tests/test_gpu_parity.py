@@ -317,3 +317,29 @@ def test_permutation_importance_matches_sklearn(pkg, published, clf_for, torch_c
     assert np.array_equal(got.importances.shape, ref.importances.shape)
     assert np.abs(got.importances - ref.importances).max() < 1e-12        # accuracies are integer counts / n
     assert np.abs(got.importances_mean - ref.importances_mean).max() < 1e-12
+
+
+def test_device_metrics_match_sklearn(pkg, published, clf_for, torch_cuda):
+    """train_ensemble_public.py:63-64,67,79: classification_report numbers exact, ROC / PR areas to the bin width."""
+    from sklearn import metrics as skm
+    torch = torch_cuda
+    clf = clf_for(published)
+    n = 200_000
+    X = pkg.synth.host_rows(published["specs"], 12, 0, n)
+    x = clf.to_device_colmajor(X)
+    proba = clf.predict_proba_device(x, n=n)
+    p1 = proba[:, 1].cpu().numpy()
+    rng = np.random.default_rng(1)
+    y = (p1.astype(np.float64) > rng.random(n)).astype(np.uint8)
+    conf, hist = pkg.metrics.device_counts(proba, torch.from_numpy(y).cuda(), threshold=0.5)
+    yy = p1 > 0.5                                                   # train:63
+    assert np.array_equal(conf, skm.confusion_matrix(y, yy))
+    want = skm.classification_report(y, yy, output_dict=True)      # train:64
+    got = pkg.metrics.binary_report(conf)
+    for key in ("0", "1", "macro avg", "weighted avg"):
+        for k2 in ("precision", "recall", "f1-score", "support"):
+            assert abs(got[key][k2] - want[key][k2]) < 1e-12
+    assert abs(got["accuracy"] - want["accuracy"]) < 1e-12
+    assert int(hist.sum()) == n
+    assert abs(pkg.metrics.roc_auc(hist) - skm.roc_auc_score(y, p1)) < 2e-5
+    assert abs(pkg.metrics.average_precision(hist) - skm.average_precision_score(y, p1)) < 1e-4

@@ -126,6 +126,62 @@ __global__ void __launch_bounds__(128, 4) k_loop_svpair(const float4* __restrict
     out[blockIdx.x * blockDim.x + threadIdx.x] = acc64[0] + acc64[1] + acc64[2] + acc64[3];
 }
 
+// SV-paired formulation: the FFMA2 pair runs over two support vectors (natural .xy/.zw halves of the LDS.128), the row's
+// z value is the broadcast scalar, so four consecutive FFMA2s (the four rows) share the 64-bit weight operand.
+template <int RING, bool SNAKE>
+__global__ void __launch_bounds__(128, 2) k_loop_svpair8(const float4* __restrict__ tabg, const float* __restrict__ zin, double* out, int groups, int reps) {
+    extern __shared__ float4 s_sv[];
+    for (int i = threadIdx.x; i < groups * STEPS + 4; i += blockDim.x) s_sv[i] = tabg[i];
+    __syncthreads();
+    constexpr int R = 8;
+    float z[F][R];
+    for (int f = 0; f < F; ++f) for (int r = 0; r < R; ++r) z[f][r] = zin[f * 8 + r + (threadIdx.x & 1)];
+    double acc64[R] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int rep = 0; rep < reps; ++rep) {
+        const float4* tab = s_sv;
+        float4 ring[RING];
+#pragma unroll
+        for (int i = 0; i < RING - 1; ++i) ring[i] = tab[i];
+#pragma unroll 1
+        for (int g = 0; g < groups; ++g) {
+            float2 t2[2][R];          // [sv pair][row]
+#pragma unroll
+            for (int st = 0; st < STEPS; ++st) {
+                ring[(st + RING - 1) % RING] = tab[st + RING - 1];
+                const float4 w4 = ring[st % RING];
+                const float2 wp[2] = {make_float2(w4.x, w4.y), make_float2(w4.z, w4.w)};
+                if (st == 0) {
+#pragma unroll
+                    for (int h = 0; h < 2; ++h)
+#pragma unroll
+                        for (int r = 0; r < R; ++r) t2[h][r] = __fmul2_rn(wp[h], make_float2(z[0][r], z[0][r]));
+                } else if (st < F) {
+#pragma unroll
+                    for (int h = 0; h < 2; ++h)
+#pragma unroll
+                        for (int rr = 0; rr < R; ++rr) {
+                            const int r = (SNAKE && h == 1) ? R - 1 - rr : rr;
+                            t2[h][r] = __ffma2_rn(wp[h], make_float2(z[st][r], z[st][r]), t2[h][r]);
+                        }
+                } else {
+#pragma unroll
+                    for (int r = 0; r < R; ++r) {
+                        float2 a2 = make_float2(0.f, 0.f);
+#pragma unroll
+                        for (int h = 0; h < 2; ++h) {
+                            float2 e = make_float2(ex2(t2[h][r].x), ex2(t2[h][r].y));
+                            a2 = __ffma2_rn(e, wp[h], a2);
+                        }
+                        acc64[r] += (double)(a2.x + a2.y);
+                    }
+                }
+            }
+            tab += STEPS;
+        }
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = acc64[0] + acc64[1] + acc64[2] + acc64[3] + acc64[4] + acc64[5] + acc64[6] + acc64[7];
+}
+
 template <typename K>
 void run(const char* name, K k, float4* tab, float* z, double* out) {
     const int blocks = 148 * 4, threads = 128, reps = 40;
@@ -154,6 +210,18 @@ int main() {
     run("SV-paired, ring 3", k_loop_svpair<3, false>, tab, z, out);
     run("SV-paired, ring 3, snake", k_loop_svpair<3, true>, tab, z, out);
     run("SV-paired, ring 2", k_loop_svpair<2, false>, tab, z, out);
+    {
+        auto k = k_loop_svpair8<3, true>;
+        const int blocks = 148 * 2, threads = 128, reps = 40;
+        size_t smem = (GROUPS * STEPS + 4) * sizeof(float4);
+        cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+        cudaEvent_t a, b; cudaEventCreate(&a); cudaEventCreate(&b);
+        k<<<blocks, threads, smem>>>(tab, z, out, GROUPS, 2); cudaDeviceSynchronize();
+        cudaEventRecord(a); k<<<blocks, threads, smem>>>(tab, z, out, GROUPS, reps); cudaEventRecord(b); cudaEventSynchronize(b);
+        float ms; cudaEventElapsedTime(&ms, a, b);
+        double ffma2 = (double)blocks * threads * reps * GROUPS * 288.0;
+        printf("%-34s %.3f ms  FMA pipe %.1f %%  (%s)\n", "SV-paired R=8, 8 warps/SM", ms, 100.0 * ffma2 * 2 / (ms * 1e-3) / 1.92e9 / 148 / 128, cudaGetErrorString(cudaGetLastError()));
+    }
     run("full, ring 2", k_loop<true, true, true, 2>, tab, z, out);
     run("full, ring 4", k_loop<true, true, true, 4>, tab, z, out);
     return 0;
