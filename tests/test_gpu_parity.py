@@ -343,3 +343,57 @@ def test_device_metrics_match_sklearn(pkg, published, clf_for, torch_cuda):
     assert int(hist.sum()) == n
     assert abs(pkg.metrics.roc_auc(hist) - skm.roc_auc_score(y, p1)) < 2e-5
     assert abs(pkg.metrics.average_precision(hist) - skm.average_precision_score(y, p1)) < 1e-4
+
+
+def test_work_list_overflow_falls_back_to_float64(pkg, published, clf_for, torch_cuda):
+    """More flagged rows than the per-call work list holds: the status word says so and the facade reruns in float64."""
+    torch = torch_cuda
+    clf = clf_for(published)
+    g = published["golden"]
+    edge = g["X"][int(g["n_appendix"]) + 1024:].astype(np.float64)          # rows next to a discontinuity
+    x = clf.to_device_colmajor(edge)
+    st = clf.new_status()
+    clf.predict_proba_device(x, n=edge.shape[0], status=st)
+    torch.cuda.synchronize()
+    flagged = edge[np.sort(st[4:4 + int(st[2])].cpu().numpy())]
+    assert flagged.shape[0] >= 1
+    reps = pkg.capi.WORKLIST_CAPACITY // flagged.shape[0] + 2
+    big = np.tile(flagged, (reps, 1))                                         # > 65532 rows, every one flagged
+    xb = clf.to_device_colmajor(big)
+    clf.predict_proba_device(xb, n=big.shape[0], status=st)
+    torch.cuda.synchronize()
+    assert int(st[0].item()) & pkg.capi.WORKLIST_OVERFLOW
+    want = np.tile(so.predict_proba(published["arrays"], flagged), (reps, 1))
+    assert np.abs(clf.predict_proba(big) - want).max() <= PROBA_TOL           # host path: automatic float64 rerun
+    got = clf.predict_proba_pinned(torch.from_numpy(big.astype(np.float32)).pin_memory()).numpy()
+    assert np.abs(got - want).max() <= PROBA_TOL
+    assert np.array_equal(clf.predict(big), np.tile(so.predict(published["arrays"], flagged), reps))
+
+
+def test_large_support_vector_tables(pkg, published, torch_cuda):
+    """A support-vector table beyond 48 KB of shared memory (opt-in dynamic smem), and the documented size limit."""
+    import copy
+    rng = np.random.default_rng(11)
+    base = published["arrays"]
+
+    def with_svs(n_sv):
+        arrays = copy.deepcopy(base)
+        svc = arrays.members[0]
+        pick = rng.integers(0, svc.sv.shape[0], n_sv)
+        svc.sv = svc.sv[pick] + rng.normal(0, 0.05, (n_sv, 17))
+        svc.dual_coef = svc.dual_coef[pick] * (434.0 / n_sv)
+        n0 = int((svc.dual_coef <= 0).sum())
+        order = np.argsort(svc.dual_coef > 0, kind="stable")
+        svc.sv, svc.dual_coef = svc.sv[order], svc.dual_coef[order]
+        svc.n_support = np.array([n0, n_sv - n0])
+        return arrays
+
+    arrays = with_svs(1203)
+    clf = pkg.HFStackB200.from_arrays(arrays)
+    X = pkg.synth.host_rows(published["specs"], 13, 0, 6000).astype(np.float64)
+    assert np.abs(clf.predict_proba(X) - so.predict_proba(arrays, X)).max() <= PROBA_TOL
+    assert np.array_equal(clf.predict(X), so.predict(arrays, X))
+    clf.close()
+    too_big = pkg.HFStackB200.from_arrays(with_svs(1600))
+    with pytest.raises(pkg.capi.HfeError, match="support vectors"):
+        too_big.predict_proba(X[:8])
