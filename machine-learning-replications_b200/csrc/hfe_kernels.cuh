@@ -40,6 +40,16 @@ constexpr int TREE_CHUNK = 16;            // float32 partial sums over trees are
 #define HFE_MIN_BLOCKS 4                  // resident blocks per SM the fused kernel is compiled for (128-register cap)
 #endif
 
+// -DHFE_BOUNDS_CHECK builds a library whose every access to the feature matrix, the permutation index and the outputs
+// is checked against the extents the caller declared; a violation traps (the launch then fails with an error).  The
+// test-suite runs its ragged / permuted / tiny cases against that build (compute-sanitizer is not available on the
+// test pool).
+#ifdef HFE_BOUNDS_CHECK
+#define HFE_ASSERT_IN(cond) do { if (!(cond)) __trap(); } while (0)
+#else
+#define HFE_ASSERT_IN(cond) do { } while (0)
+#endif
+
 __device__ __forceinline__ float ex2_approx(float x) {
     float y;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -222,6 +232,7 @@ __device__ __noinline__ RowResult finish_row(const ScoreParams& P, bool has_svc,
 
 __device__ __forceinline__ void store_row(const ScoreParams& P, long long row, const RowResult& r,
                                           bool write_out = true) {
+    HFE_ASSERT_IN(row >= 0 && row < P.n);
     if (P.out && write_out) {
         P.out[2 * row] = (float)(1.0 - r.p1);
         P.out[2 * row + 1] = (float)r.p1;
@@ -240,7 +251,9 @@ __device__ __forceinline__ void store_row(const ScoreParams& P, long long row, c
 }
 
 __device__ __forceinline__ float load_feature(const ScoreParams& P, int f, long long row) {
+    HFE_ASSERT_IN(row >= 0 && row < P.n && f >= 0 && f < F);
     long long src = (f == P.perm_col) ? (long long)P.perm_idx[row] : row;
+    HFE_ASSERT_IN(src >= 0 && src < P.n);
     return __ldg(P.x + (long long)f * P.ld + src);
 }
 
@@ -248,20 +261,26 @@ __device__ __forceinline__ float load_feature(const ScoreParams& P, int f, long 
 // and ld is a multiple of 4 not below n.  It is kept free of control flow so that a thread's 17 column loads can all
 // be in flight at once; fix_rows4 patches the rare cases afterwards.
 __device__ __forceinline__ float4 load_rows4(const ScoreParams& P, int f, long long row0) {
+    HFE_ASSERT_IN(row0 >= 0 && row0 + 3 < P.ld && row0 < P.n && (row0 & 3) == 0);
     return __ldg(reinterpret_cast<const float4*>(P.x + (long long)f * P.ld + row0));
 }
 
 // Rows at or beyond n (ragged last tile) read padding and are zeroed; a permuted column is gathered through perm_idx.
-__device__ __forceinline__ float4 fix_rows4(const ScoreParams& P, int f, long long row0, bool full, float4 v) {
+// ``row_ld`` is the row the loads use (threads whose whole quad lies beyond n load quad 0 instead, so every address
+// stays inside the matrix); ``row0`` is the thread's real first row.
+__device__ __forceinline__ float4 fix_rows4(const ScoreParams& P, int f, long long row0, long long row_ld, bool full,
+                                            float4 v) {
     if (f == P.perm_col) {
         const float* col = P.x + (long long)f * P.ld;
-        const int* idx = P.perm_idx + row0;
+        const int* idx = P.perm_idx + row_ld;
+        HFE_ASSERT_IN(row_ld >= 0 && row_ld < P.n && __ldg(idx) >= 0 && __ldg(idx) < P.n);
         v.x = __ldg(col + __ldg(idx));
-        if (full || row0 + 1 < P.n) v.y = __ldg(col + __ldg(idx + 1));
-        if (full || row0 + 2 < P.n) v.z = __ldg(col + __ldg(idx + 2));
-        if (full || row0 + 3 < P.n) v.w = __ldg(col + __ldg(idx + 3));
+        if (full || row_ld + 1 < P.n) v.y = __ldg(col + __ldg(idx + 1));
+        if (full || row_ld + 2 < P.n) v.z = __ldg(col + __ldg(idx + 2));
+        if (full || row_ld + 3 < P.n) v.w = __ldg(col + __ldg(idx + 3));
     }
     if (!full) {
+        if (row0 + 0 >= P.n) v.x = 0.f;
         if (row0 + 1 >= P.n) v.y = 0.f;
         if (row0 + 2 >= P.n) v.z = 0.f;
         if (row0 + 3 >= P.n) v.w = 0.f;
@@ -401,6 +420,7 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
     constexpr int R = ROWS_PER_THREAD;
 
     const bool full = (row0 + R <= P.n);
+    const long long row_ld = row0 < P.n ? row0 : 0;      // out-of-range threads of the last tile load quad 0
     double raw[R], zl[R];
     float zz32[R];
     float zs[F][R];                 // standardised features, one scalar register per (feature, row)
@@ -417,7 +437,7 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
         // a window of STREAM_WINDOW feature columns is kept in flight: column f+W is requested before column f is used
         // (measured on B200, 10 M rows: W=6/32 warps 50 %, W=12/20 warps 52 %, W=17/16 warps 56 % of HBM copy bandwidth)
         constexpr int W = STREAM_WINDOW;
-        auto load_col = [&](int f) -> float4 { return load_rows4(P, f, row0); };
+        auto load_col = [&](int f) -> float4 { return load_rows4(P, f, row_ld); };
         const bool needs_fix = !full || P.perm_col >= 0;
         float4 win[W];
 #pragma unroll
@@ -426,7 +446,7 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
         for (int f = 0; f < F; ++f) {
             float4 v = win[f % W];
             if (f + W < F) win[f % W] = load_col(f + W);
-            if (needs_fix) v = fix_rows4(P, f, row0, full, v);
+            if (needs_fix) v = fix_rows4(P, f, row0, row_ld, full, v);
             float xf[R];
             xf[0] = v.x; xf[1] = v.y; xf[2] = v.z; xf[3] = v.w;
 #pragma unroll
@@ -459,13 +479,13 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
     float xv[F][R];
 #pragma unroll
     for (int f = 0; f < F; ++f) {
-        float4 v = load_rows4(P, f, row0);
+        float4 v = load_rows4(P, f, row_ld);
         xv[f][0] = v.x; xv[f][1] = v.y; xv[f][2] = v.z; xv[f][3] = v.w;
     }
     if (!full || P.perm_col >= 0) {              // rare: ragged last tile, or a permutation-importance pass
 #pragma unroll
         for (int f = 0; f < F; ++f) {
-            float4 v = fix_rows4(P, f, row0, full, make_float4(xv[f][0], xv[f][1], xv[f][2], xv[f][3]));
+            float4 v = fix_rows4(P, f, row0, row_ld, full, make_float4(xv[f][0], xv[f][1], xv[f][2], xv[f][3]));
             xv[f][0] = v.x; xv[f][1] = v.y; xv[f][2] = v.z; xv[f][3] = v.w;
         }
     }

@@ -397,3 +397,18 @@ def test_large_support_vector_tables(pkg, published, torch_cuda):
     too_big = pkg.HFStackB200.from_arrays(with_svs(1600))
     with pytest.raises(pkg.capi.HfeError, match="support vectors"):
         too_big.predict_proba(X[:8])
+
+
+def test_bounds_checked_build_on_small_and_ragged_cases(cuda_lib):
+    """Every kernel at tiny / ragged sizes against the library built with -DHFE_BOUNDS_CHECK: any access outside the
+    declared extents of x, perm_idx or the outputs traps and the run fails (stands in for compute-sanitizer)."""
+    import os
+    import subprocess
+    import sys
+    from conftest import ROOT
+    checked = os.path.join(ROOT, "machine-learning-replications_b200", "libhfe_checked.so")
+    assert os.path.exists(checked), "build() did not produce the bounds-checked library"
+    env = dict(os.environ, HFE_LIB=checked)
+    res = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "sanitize_target.py")], env=env,
+                         capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0 and "sanitize target done" in res.stdout, res.stderr[-2000:]
