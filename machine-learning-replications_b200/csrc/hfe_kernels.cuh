@@ -292,16 +292,15 @@ __device__ __forceinline__ float4 fix_rows4(const ScoreParams& P, int f, long lo
 // (global node index).
 template <typename XGet>
 __device__ __forceinline__ int walk_tree(const ScoreParams& P, int t, XGet xget) {
-    int base = P.tree_off[t];
     int depth = P.tree_depth[t];
-    int node = 0;
+    unsigned node = (unsigned)P.tree_off[t];
     for (int lvl = 0; lvl < depth; ++lvl) {
-        uint2 nd = __ldg(P.nodes + base + node);
+        uint2 nd = __ldg(P.nodes + node);
         float thr = __uint_as_float(nd.x);
         float xv = xget(nd.y >> 24);
-        node = (int)(nd.y & 0xFFFFFFu) + (xv > thr ? 1 : 0);
+        node = (nd.y & 0xFFFFFFu) + (xv > thr ? 1u : 0u);
     }
-    return base + node;
+    return (int)node;
 }
 
 // Cooperative float64 evaluation of one row by one warp -- the exact-arithmetic path.  Follows the reference's
@@ -333,14 +332,13 @@ __device__ __noinline__ bool eval_row_f64_warp(const ScoreParams& P, long long r
     if (has_gbt) {
         for (int t0 = 0; t0 < P.n_trees; t0 += 32) {          // uniform trip counts: every lane joins every shuffle
             const int t = min(t0 + lane, P.n_trees - 1);
-            const int base = P.tree_off[t];
-            int node = 0;
+            unsigned node = (unsigned)P.tree_off[t];
             for (int lvl = 0; lvl < P.max_depth; ++lvl) {       // leaves self-loop, so walking past a leaf is harmless
-                uint2 nd = __ldg(P.nodes + base + node);
+                uint2 nd = __ldg(P.nodes + node);
                 float xv = __shfl_sync(full_mask, x_mine, (int)(nd.y >> 24));
-                node = (int)(nd.y & 0xFFFFFFu) + (xv > __uint_as_float(nd.x) ? 1 : 0);
+                node = (nd.y & 0xFFFFFFu) + (xv > __uint_as_float(nd.x) ? 1u : 0u);
             }
-            if (t0 + lane < P.n_trees) part_gbt += P.value64[base + node];
+            if (t0 + lane < P.n_trees) part_gbt += P.value64[node];
         }
     }
 #pragma unroll
@@ -538,36 +536,45 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
 
     // ---- general boosted trees: predicated fixed-depth walk, x from this thread's shared-memory slots ----------------
     if (TREE_MODE == 2) {
-        // own rows only: no barrier needed between the s_xt stores above and these loads
+        // own rows only: no barrier needed between the s_xt stores above and these loads.  Two trees are walked at a
+        // time, so a thread keeps 2 x R independent node chains in flight (the walk is bound by L1 latency).
 #pragma unroll
         for (int r = 0; r < R; ++r) raw[r] = P.gbt_init;
+        const float* xs = s_xt + tid;
         for (int t0 = 0; t0 < P.n_trees; t0 += TREE_CHUNK) {
             float acc[R];
 #pragma unroll
             for (int r = 0; r < R; ++r) acc[r] = 0.f;
-            int t1 = min(t0 + TREE_CHUNK, P.n_trees);
-            for (int t = t0; t < t1; ++t) {
-                int base = P.tree_off[t];
-                int depth = P.tree_depth[t];
-                int node[R];
+            const int t1 = min(t0 + TREE_CHUNK, P.n_trees);
+            for (int t = t0; t < t1; t += 2) {
+                const bool two = t + 1 < t1;
+                const int tb = two ? t + 1 : t;
+                const unsigned root_a = (unsigned)P.tree_off[t], root_b = (unsigned)P.tree_off[tb];
+                const int depth = max((int)P.tree_depth[t], (int)P.tree_depth[tb]);
+                unsigned ia[R], ib[R];           // global node indices (children are stored as global indices too)
 #pragma unroll
-                for (int r = 0; r < R; ++r) node[r] = 0;
+                for (int r = 0; r < R; ++r) { ia[r] = root_a; ib[r] = root_b; }
                 for (int lvl = 0; lvl < depth; ++lvl) {
 #pragma unroll
                     for (int r = 0; r < R; ++r) {
-                        uint2 nd = __ldg(P.nodes + base + node[r]);
-                        float x = s_xt[(nd.y >> 24) * BLOCK_ROWS + r * BLOCK_THREADS + tid];
-                        node[r] = (int)(nd.y & 0xFFFFFFu) + (x > __uint_as_float(nd.x) ? 1 : 0);
+                        const uint2 da = __ldg(P.nodes + ia[r]);
+                        const uint2 db = __ldg(P.nodes + ib[r]);
+                        const float xa = xs[(da.y >> 24) * BLOCK_ROWS + r * BLOCK_THREADS];
+                        const float xb = xs[(db.y >> 24) * BLOCK_ROWS + r * BLOCK_THREADS];
+                        ia[r] = (da.y & 0xFFFFFFu) + (xa > __uint_as_float(da.x) ? 1u : 0u);
+                        ib[r] = (db.y & 0xFFFFFFu) + (xb > __uint_as_float(db.x) ? 1u : 0u);
                     }
                 }
 #pragma unroll
-                for (int r = 0; r < R; ++r) acc[r] += __ldg(P.value32 + base + node[r]);
+                for (int r = 0; r < R; ++r) {
+                    acc[r] += __ldg(P.value32 + ia[r]);
+                    if (two) acc[r] += __ldg(P.value32 + ib[r]);
+                }
             }
 #pragma unroll
             for (int r = 0; r < R; ++r) raw[r] += (double)acc[r];
         }
     }
-
 
     // Links of the tree and logistic members now, so that only their share of the combiner's logit (one double per
     // row) has to stay in registers across the RBF loop.

@@ -85,7 +85,7 @@ struct ScoreParams {
     int split_begin[F + 1];
     float split_thr[MAX_SPLITS];
     float split_delta[MAX_SPLITS];
-    const uint2* nodes;         // {thr32 bits, feature<<24 | child}, tree-local child index
+    const uint2* nodes;         // {thr32 bits, feature<<24 | child}: child = GLOBAL index of the left child (right = +1)
     const float* value32;       // lr * value, per node
     const double* value64;
     const int* tree_off;        // [n_trees+1]
@@ -349,7 +349,7 @@ inline int build_gbt(Model* m, const ParsedBlob& pb, uint32_t idx) {
     if (!ps || !all_finite(ps->f64(), 4)) return fail(HFE_ERR_BAD_BLOB, "blob: boosting params missing");
     const double* p = ps->f64();
     double init_raw = p[0], lr = p[1];
-    if (!(p[2] >= 1 && p[2] <= 1e6 && p[3] >= 1 && p[3] < 2147483648.0))
+    if (!(p[2] >= 1 && p[2] <= 1e6 && p[3] >= 1 && p[3] < 16777216.0))      // 24-bit global node indices
         return fail(HFE_ERR_BAD_BLOB, "blob: bad tree counts");
     int n_trees = (int)p[2];
     int64_t n_nodes = (int64_t)p[3];
@@ -435,12 +435,12 @@ inline int build_gbt(Model* m, const ParsedBlob& pb, uint32_t idx) {
                 float inf = INFINITY;
                 uint32_t bits;
                 std::memcpy(&bits, &inf, 4);
-                nodes[q] = make_uint2(bits, (uint32_t)newpos[i]);    // self loop: x > +inf is never true
+                nodes[q] = make_uint2(bits, (uint32_t)q);            // self loop: x > +inf is never true
             } else {
                 float t32 = floor_to_f32(T[i]);
                 uint32_t bits;
                 std::memcpy(&bits, &t32, 4);
-                nodes[q] = make_uint2(bits, ((uint32_t)Fe[i] << 24) | (uint32_t)newpos[L[i]]);
+                nodes[q] = make_uint2(bits, ((uint32_t)Fe[i] << 24) | (uint32_t)(base + newpos[L[i]]));
             }
         }
         bool stump = (cnt == 3 && L[0] != -1 && L[L[0]] == -1 && L[R[0]] == -1);

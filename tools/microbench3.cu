@@ -73,7 +73,7 @@ __global__ void __launch_bounds__(128, 4) k_loop(const float4* __restrict__ tabg
 
 // SV-paired formulation: the FFMA2 pair runs over two support vectors (natural .xy/.zw halves of the LDS.128), the row's
 // z value is the broadcast scalar, so four consecutive FFMA2s (the four rows) share the 64-bit weight operand.
-template <int RING, bool SNAKE>
+template <int RING, bool SNAKE, bool NOLDS = false, bool NOMUFU = false>
 __global__ void __launch_bounds__(128, 4) k_loop_svpair(const float4* __restrict__ tabg, const float* __restrict__ zin, double* out, int groups, int reps) {
     extern __shared__ float4 s_sv[];
     for (int i = threadIdx.x; i < groups * STEPS + 4; i += blockDim.x) s_sv[i] = tabg[i];
@@ -86,12 +86,13 @@ __global__ void __launch_bounds__(128, 4) k_loop_svpair(const float4* __restrict
         float4 ring[RING];
 #pragma unroll
         for (int i = 0; i < RING - 1; ++i) ring[i] = tab[i];
+        if (NOLDS) ring[RING - 1] = tab[RING - 1];
 #pragma unroll 1
         for (int g = 0; g < groups; ++g) {
             float2 t2[2][R];          // [sv pair][row]
 #pragma unroll
             for (int st = 0; st < STEPS; ++st) {
-                ring[(st + RING - 1) % RING] = tab[st + RING - 1];
+                if (!NOLDS) ring[(st + RING - 1) % RING] = tab[st + RING - 1];
                 const float4 w4 = ring[st % RING];
                 const float2 wp[2] = {make_float2(w4.x, w4.y), make_float2(w4.z, w4.w)};
                 if (st == 0) {
@@ -113,7 +114,7 @@ __global__ void __launch_bounds__(128, 4) k_loop_svpair(const float4* __restrict
                         float2 a2 = make_float2(0.f, 0.f);
 #pragma unroll
                         for (int h = 0; h < 2; ++h) {
-                            float2 e = make_float2(ex2(t2[h][r].x), ex2(t2[h][r].y));
+                            float2 e = NOMUFU ? __fmul2_rn(t2[h][r], make_float2(0.5f, 0.5f)) : make_float2(ex2(t2[h][r].x), ex2(t2[h][r].y));
                             a2 = __ffma2_rn(e, wp[h], a2);
                         }
                         acc64[r] += (double)(a2.x + a2.y);
@@ -121,6 +122,7 @@ __global__ void __launch_bounds__(128, 4) k_loop_svpair(const float4* __restrict
                 }
             }
             tab += STEPS;
+            if (NOLDS) { ring[0].x += 1e-7f; ring[1].y += 1e-7f; ring[2].z += 1e-7f; }   // keep the group loop from being hoisted
         }
     }
     out[blockIdx.x * blockDim.x + threadIdx.x] = acc64[0] + acc64[1] + acc64[2] + acc64[3];
@@ -210,6 +212,9 @@ int main() {
     run("SV-paired, ring 3", k_loop_svpair<3, false>, tab, z, out);
     run("SV-paired, ring 3, snake", k_loop_svpair<3, true>, tab, z, out);
     run("SV-paired, ring 2", k_loop_svpair<2, false>, tab, z, out);
+    run("SV-paired snake, NO LDS in loop", k_loop_svpair<3, true, true>, tab, z, out);
+    run("SV-paired snake, NO LDS, NO MUFU", k_loop_svpair<3, true, true, true>, tab, z, out);
+    run("SV-paired snake, LDS, NO MUFU", k_loop_svpair<3, true, false, true>, tab, z, out);
     {
         auto k = k_loop_svpair8<3, true>;
         const int blocks = 148 * 2, threads = 128, reps = 40;
