@@ -152,6 +152,22 @@ int hfe_model_create(const void* blob, size_t blob_bytes, int device, hfe_model*
     Model* impl = nullptr;
     int rc = build_model(reinterpret_cast<const uint8_t*>(copy.data()), blob_bytes, device, &impl);
     if (rc) return rc;
+    {   // staging arena for small host batches: all optional outputs of SMALL_HOST_ROWS rows + both status arrays
+        auto up = [](size_t b) { return (b + 255) & ~(size_t)255; };
+        size_t rows = SMALL_HOST_ROWS;
+        size_t bytes = up(rows * F * sizeof(double)) + up(rows * F * sizeof(float)) + up(rows * 2 * sizeof(float)) +
+                       up(rows * sizeof(double)) + up(rows * MAX_MEMBERS * sizeof(double)) + up(rows) +
+                       up((HFE_STATUS_WORDS + HFE_STATUS_HEADER_WORDS) * sizeof(uint32_t)) + 256;
+        void* p = nullptr;
+        if (cudaMalloc(&p, bytes) == cudaSuccess) {
+            impl->small_arena = static_cast<unsigned char*>(p);
+            impl->small_arena_bytes = bytes;
+            impl->allocations.push_back(p);
+            impl->device_bytes += bytes;
+        } else {
+            cudaGetLastError();                 // no arena: small calls fall back to per-call allocation
+        }
+    }
     hfe_model* h = new (std::nothrow) hfe_model{impl};
     if (!h) return fail(HFE_ERR_INVALID_ARGUMENT, "out of host memory");
     *out_model = h;
@@ -339,8 +355,15 @@ int hfe_predict_host(const hfe_model* model, const double* x_rowmajor, int64_t n
     size_t total = up(in_bytes) + up(col_bytes) + up(out_bytes) + up(dec_bytes) + up(meta_bytes) + up(lab_bytes) +
                    up(status_bytes) + 256;
     unsigned char* buf = nullptr;
-    HFE_CUDA_TRY(cudaMalloc(&buf, total));
-    struct Guard { unsigned char* p; ~Guard() { cudaFree(p); } } guard{buf};
+    std::unique_lock<std::mutex> small_lock(m->small_mutex, std::defer_lock);
+    struct Guard { unsigned char* p; ~Guard() { if (p) cudaFree(p); } } guard{nullptr};
+    if (n <= SMALL_HOST_ROWS && m->small_arena && total <= m->small_arena_bytes) {
+        small_lock.lock();                      // the arena is shared by all small host calls on this handle
+        buf = m->small_arena;
+    } else {
+        HFE_CUDA_TRY(cudaMalloc(&buf, total));
+        guard.p = buf;
+    }
     unsigned char* cur = buf;
     auto take = [&](size_t b) { unsigned char* p = cur; cur += up(b); return p; };
     double* d_in = reinterpret_cast<double*>(take(in_bytes));

@@ -22,6 +22,7 @@
 #include <cstdint>
 #include <cstring>
 #include <map>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -36,6 +37,7 @@ constexpr int MAX_SPLITS = 128;       // merged stump table capacity (kernel par
 constexpr int SV_GROUP = 4;           // support vectors per inner tile
 constexpr int SV_STEPS = F + 1;       // float4 steps per group: F weight steps + one folded-coefficient step
 constexpr int SV_PAD_ROWS = 2;        // zero steps after the table so the 2-step-ahead prefetch may over-read
+constexpr int SMALL_HOST_ROWS = 4096;   // host batches up to this size use the model's preallocated staging arena
 constexpr int MAX_EDGES = 16;          // coupling-solver discontinuities (6 exist for eps = 0.0025)
 #ifndef HFE_SV_CHUNK
 #define HFE_SV_CHUNK 4
@@ -113,6 +115,11 @@ struct Model {
     ScoreParams base{};           // request fields zero; table pointers filled
     std::vector<void*> allocations;
     uint64_t device_bytes = 0;
+    // staging for small host batches (hfe_predict_host with n <= SMALL_HOST_ROWS): allocated once with the model so a
+    // single-patient call (predict_hf.py) pays no cudaMalloc / cudaFree; one caller at a time (mutex)
+    mutable std::mutex small_mutex;
+    unsigned char* small_arena = nullptr;
+    size_t small_arena_bytes = 0;
 };
 
 inline thread_local std::string g_last_error;
