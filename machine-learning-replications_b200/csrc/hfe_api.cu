@@ -356,12 +356,12 @@ int hfe_predict_host(const hfe_model* model, const double* x_rowmajor, int64_t n
                    up(status_bytes) + 256;
     unsigned char* buf = nullptr;
     std::unique_lock<std::mutex> small_lock(m->small_mutex, std::defer_lock);
-    struct Guard { unsigned char* p; ~Guard() { if (p) cudaFree(p); } } guard{nullptr};
+    struct Guard { unsigned char* p; ~Guard() { if (p) cudaFreeAsync(p, nullptr); } } guard{nullptr};
     if (n <= SMALL_HOST_ROWS && m->small_arena && total <= m->small_arena_bytes) {
         small_lock.lock();                      // the arena is shared by all small host calls on this handle
         buf = m->small_arena;
     } else {
-        HFE_CUDA_TRY(cudaMalloc(&buf, total));
+        HFE_CUDA_TRY(cudaMallocAsync(&buf, total, nullptr));     // stream-ordered pool: no device-wide sync per call
         guard.p = buf;
     }
     unsigned char* cur = buf;

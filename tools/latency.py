@@ -17,3 +17,12 @@ for name, f in (("b200 facade", clf.predict_proba), ("scikit-learn", sk.predict_
         t0 = time.perf_counter(); f(x); t.append(time.perf_counter() - t0)
     t.sort()
     print(f"{name:14s} 1 patient: median {1e6 * t[100]:.1f} us, p95 {1e6 * t[190]:.1f} us  -> {100 * f(x)[0, 1]:.2f} %")
+
+X = P.synth.host_rows(P.synth.schema_specs(), 1, 0, 10_000).astype(np.float64)      # BASELINE config 1: 10 k patients
+for name, f in (("b200 facade", clf.predict_proba), ("scikit-learn", sk.predict_proba)):
+    for _ in range(3): f(X)
+    t = []
+    for _ in range(20):
+        t0 = time.perf_counter(); f(X); t.append(time.perf_counter() - t0)
+    t.sort()
+    print(f"{name:14s} 10 000 patients: median {1e3 * t[10]:.3f} ms")
