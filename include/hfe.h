@@ -69,7 +69,8 @@ typedef struct hfe_model_info {
     int32_t tree_mode;             /* 0 none, 1 depth-1 stumps merged into a split table, 2 general node tables */
     int32_t n_merged_splits;
     int32_t device;
-    int32_t reserved;
+    int32_t rbf_fma_per_row;       /* float32 lane-FMAs the fused kernel executes per row in its RBF loop (table steps x 4
+                                    * lanes); below n_support_vectors * 18 when the prefix-shared layout is in use */
     double  svc_guard;             /* |decision value| uncertainty assumed for the float32 RBF sum */
     uint64_t device_bytes;         /* bytes of device memory the handle owns */
 } hfe_model_info;

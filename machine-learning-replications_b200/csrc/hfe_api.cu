@@ -26,13 +26,12 @@ int check_matrix(const hfe_model* model, const float* x, int64_t n, int64_t ld) 
     return HFE_OK;
 }
 
-template <bool SVC, int TM>
+template <bool SVC, int TM, bool PFX>
 int launch_score(const Model* m, const ScoreParams& P, cudaStream_t stream) {
-    if (SVC && P.n_groups > MAX_SMEM_GROUPS)
-        return fail(HFE_ERR_UNSUPPORTED, "more than 1536 support vectors do not fit one block's shared memory");
-    size_t smem = (SVC ? ((size_t)P.n_groups * SV_STEPS + SV_PAD_ROWS) * sizeof(float4) : 0) +
-                  (TM == 2 ? (size_t)F * BLOCK_ROWS * sizeof(float) : 0);
-    auto kernel = hfe_score_kernel<SVC, TM>;
+    if (SVC && P.sv_bytes > MAX_SV_TABLE_BYTES)
+        return fail(HFE_ERR_UNSUPPORTED, "the support-vector table does not fit one block's shared memory");
+    size_t smem = (SVC ? (size_t)P.sv_bytes : 0) + (TM == 2 ? (size_t)F * BLOCK_ROWS * sizeof(float) : 0);
+    auto kernel = hfe_score_kernel<SVC, TM, PFX>;
     // per device and shared-memory size: opt in to large dynamic shared memory, ask how many blocks stay resident
     static std::mutex mu;
     static std::map<std::pair<int, size_t>, int> resident;
@@ -55,20 +54,27 @@ int launch_score(const Model* m, const ScoreParams& P, cudaStream_t stream) {
     long long tiles = (P.n + WARP_ROWS - 1) / WARP_ROWS;
     long long blocks = (tiles + BLOCK_WARPS - 1) / BLOCK_WARPS;
     if (HFE_PERSISTENT || !SVC) blocks = std::min<long long>(blocks, (long long)sms * per_sm);
-    kernel<<<(unsigned)blocks, BLOCK_THREADS, smem, stream>>>(P, P.n_groups);
+    kernel<<<(unsigned)blocks, BLOCK_THREADS, smem, stream>>>(P, P.sv_bytes);
     HFE_CUDA_TRY(cudaGetLastError());
     return HFE_OK;
 }
 
 int dispatch_score(const Model* m, const ScoreParams& P, cudaStream_t stream) {
     bool svc = P.slot_svc >= 0;
+    if (svc && P.sv_quads > 0) {
+        switch (m->tree_mode) {
+            case 0: return launch_score<true, 0, true>(m, P, stream);
+            case 1: return launch_score<true, 1, true>(m, P, stream);
+            default: return launch_score<true, 2, true>(m, P, stream);
+        }
+    }
     switch (m->tree_mode * 2 + (svc ? 1 : 0)) {
-        case 0: return launch_score<false, 0>(m, P, stream);
-        case 1: return launch_score<true, 0>(m, P, stream);
-        case 2: return launch_score<false, 1>(m, P, stream);
-        case 3: return launch_score<true, 1>(m, P, stream);
-        case 4: return launch_score<false, 2>(m, P, stream);
-        default: return launch_score<true, 2>(m, P, stream);
+        case 0: return launch_score<false, 0, false>(m, P, stream);
+        case 1: return launch_score<true, 0, false>(m, P, stream);
+        case 2: return launch_score<false, 1, false>(m, P, stream);
+        case 3: return launch_score<true, 1, false>(m, P, stream);
+        case 4: return launch_score<false, 2, false>(m, P, stream);
+        default: return launch_score<true, 2, false>(m, P, stream);
     }
 }
 
@@ -92,7 +98,8 @@ int score_common(const hfe_model* model, const float* x, int64_t n, int64_t ld, 
     P.x = x;
     P.n = n;
     P.ld = ld;
-    P.perm_col = perm_col < 0 ? -1 : perm_col;
+    for (int f = 0; f < F; ++f) P.col_off[f] = (long long)m->col_of[f] * ld;
+    P.perm_col = perm_col < 0 ? -1 : m->internal_of[perm_col];
     P.perm_idx = perm_idx;
     P.out = out;
     P.out64 = out64;
@@ -198,6 +205,9 @@ int hfe_model_get_info(const hfe_model* model, hfe_model_info* info) {
     info->tree_mode = m->tree_mode;
     info->n_merged_splits = m->n_splits;
     info->device = m->device;
+    info->rbf_fma_per_row = m->n_sv == 0 ? 0
+                            : m->base.sv_quads > 0 ? 4 * (m->base.sv_quads * SV_PREFIX + m->sv_steps * SV_LEAF_STEPS)
+                                                   : 4 * m->base.n_groups * SV_STEPS;
     info->svc_guard = m->svc_guard;
     info->device_bytes = m->device_bytes;
     return HFE_OK;
@@ -243,6 +253,7 @@ int hfe_apply(const hfe_model* model, const float* x, int64_t n, int64_t ld, uin
     P.x = x;
     P.n = n;
     P.ld = ld;
+    for (int f = 0; f < F; ++f) P.col_off[f] = (long long)m->col_of[f] * ld;
     long long blocks = (n + BLOCK_THREADS - 1) / BLOCK_THREADS;
     hfe_apply_kernel<<<(unsigned)blocks, BLOCK_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(P, leaves);
     HFE_CUDA_TRY(cudaGetLastError());

@@ -24,7 +24,7 @@ namespace hfe {
 constexpr int BLOCK_THREADS = HFE_BLOCK_THREADS;
 constexpr int ROWS_PER_THREAD = 4;
 constexpr int BLOCK_ROWS = BLOCK_THREADS * ROWS_PER_THREAD;
-constexpr int MAX_SMEM_GROUPS = 384;      // support-vector groups staged per pass (384*18*16 B = 108 KB; 2 blocks/SM)
+constexpr int MAX_SV_TABLE_BYTES = (384 * 18 + 2) * 16;   // staged support-vector table (flat layout: 1536 vectors; 108 KB, 2 blocks/SM)
 #ifndef HFE_STREAM_WINDOW
 #define HFE_STREAM_WINDOW 17
 #endif
@@ -35,6 +35,12 @@ constexpr int TREE_CHUNK = 16;            // float32 partial sums over trees are
 #endif
 #ifndef HFE_MIN_BLOCKS_NOSVC
 #define HFE_MIN_BLOCKS_NOSVC 4            // SVC-free streaming pass: all 17 column loads of a thread in flight at once (measured best)
+#endif
+#ifndef HFE_PFX_FLUSH
+#define HFE_PFX_FLUSH 1                   // float32 partial sums go to float64 after every leaf step (1) or every 2nd (2)
+#endif
+#ifndef HFE_MIN_BLOCKS_PFX
+#define HFE_MIN_BLOCKS_PFX 4              // same, for the prefix-shared support-vector layout
 #endif
 #ifndef HFE_MIN_BLOCKS
 #define HFE_MIN_BLOCKS 4                  // resident blocks per SM the fused kernel is compiled for (128-register cap)
@@ -254,7 +260,7 @@ __device__ __forceinline__ float load_feature(const ScoreParams& P, int f, long 
     HFE_ASSERT_IN(row >= 0 && row < P.n && f >= 0 && f < F);
     long long src = (f == P.perm_col) ? (long long)P.perm_idx[row] : row;
     HFE_ASSERT_IN(src >= 0 && src < P.n);
-    return __ldg(P.x + (long long)f * P.ld + src);
+    return __ldg(P.x + P.col_off[f] + src);
 }
 
 // Four consecutive rows of one feature column.  The 128-bit load is always in bounds: row0 is a multiple of 4 below n
@@ -262,7 +268,7 @@ __device__ __forceinline__ float load_feature(const ScoreParams& P, int f, long 
 // be in flight at once; fix_rows4 patches the rare cases afterwards.
 __device__ __forceinline__ float4 load_rows4(const ScoreParams& P, int f, long long row0) {
     HFE_ASSERT_IN(row0 >= 0 && row0 + 3 < P.ld && row0 < P.n && (row0 & 3) == 0);
-    return __ldg(reinterpret_cast<const float4*>(P.x + (long long)f * P.ld + row0));
+    return __ldg(reinterpret_cast<const float4*>(P.x + P.col_off[f] + row0));
 }
 
 // Rows at or beyond n (ragged last tile) read padding and are zeroed; a permuted column is gathered through perm_idx.
@@ -271,7 +277,7 @@ __device__ __forceinline__ float4 load_rows4(const ScoreParams& P, int f, long l
 __device__ __forceinline__ float4 fix_rows4(const ScoreParams& P, int f, long long row0, long long row_ld, bool full,
                                             float4 v) {
     if (f == P.perm_col) {
-        const float* col = P.x + (long long)f * P.ld;
+        const float* col = P.x + P.col_off[f];
         const int* idx = P.perm_idx + row_ld;
         HFE_ASSERT_IN(row_ld >= 0 && row_ld < P.n && __ldg(idx) >= 0 && __ldg(idx) < P.n);
         v.x = __ldg(col + __ldg(idx));
@@ -374,13 +380,12 @@ __device__ __noinline__ bool eval_row_f64_warp(const ScoreParams& P, long long r
 constexpr int WARP_ROWS = 32 * ROWS_PER_THREAD;          // rows one warp scores per tile
 constexpr int BLOCK_WARPS = BLOCK_THREADS / 32;
 
-template <bool SVC, int TREE_MODE>
-__global__ void __launch_bounds__(BLOCK_THREADS, SVC ? HFE_MIN_BLOCKS : HFE_MIN_BLOCKS_NOSVC)
-hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
+template <bool SVC, int TREE_MODE, bool PFX>
+__global__ void __launch_bounds__(BLOCK_THREADS, SVC ? (PFX ? HFE_MIN_BLOCKS_PFX : HFE_MIN_BLOCKS) : HFE_MIN_BLOCKS_NOSVC)
+hfe_score_kernel(const __grid_constant__ ScoreParams P, int sv_bytes) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    float4* s_sv = reinterpret_cast<float4*>(smem_raw);                       // [smem_groups][SV_STEPS] (+pad)
-    float* s_xt = reinterpret_cast<float*>(smem_raw) +
-                  (SVC ? ((size_t)smem_groups * SV_STEPS + SV_PAD_ROWS) * 4 : 0);             // [F][BLOCK_ROWS]
+    float4* s_sv = reinterpret_cast<float4*>(smem_raw);                       // the support-vector table (sv_bytes)
+    float* s_xt = reinterpret_cast<float*>(smem_raw) + (SVC ? (size_t)sv_bytes / 4 : 0);      // [F][BLOCK_ROWS]
 
     const int tid = threadIdx.x;
     const int lane = tid & 31;
@@ -401,7 +406,7 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
         }
         __syncthreads();
         if (tid == 0) {
-            const unsigned bytes = (unsigned)((P.n_groups * SV_STEPS + SV_PAD_ROWS) * sizeof(float4));
+            const unsigned bytes = (unsigned)sv_bytes;
             asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(bytes) : "memory");
             asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                          ::"r"((unsigned)__cvta_generic_to_shared(s_sv)), "l"(P.sv_tab), "r"(bytes), "r"(mbar)
@@ -616,6 +621,92 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int smem_groups) {
         const float4* tab = s_sv;
         float4 ring[3];
         ring[0] = tab[0]; ring[1] = tab[1];
+        if (PFX) {
+            // Prefix-shared layout (hfe_model.cuh, build_svc): the table is one stream of float4 steps -- per quad
+            // SV_PREFIX prefix-weight steps, then count[q] leaf steps of SV_LEAF_STEPS.  The partial exponents of the
+            // prefix stay in p2 and seed every leaf step's FMA chains, so each support vector costs
+            // F - SV_PREFIX + 1 FMAs instead of F + 1.
+            //
+            // A leaf step covers two support-vector pairs, skewed by half a step so that one warp keeps both the FMA
+            // and the MUFU pipe busy: while the FMA chains of pair 0 run (phase A), the exponents pair 1 finished in
+            // the previous step go through ex2 and their coefficient FMAs; while pair 1's chains run (phase B), the
+            // same happens for the pair-0 exponents just finished.  Step layout: [coefficients][pair 0: 4 steps of two
+            // features][pair 1: 4 steps of two features].
+            static_assert((F - SV_PREFIX) == 2 * R && R == 4, "leaf step: one ex2 row per two-feature table step");
+            const unsigned char* quad_steps =
+                reinterpret_cast<const unsigned char*>(s_sv) + (size_t)sv_bytes - (((size_t)P.sv_quads + 15) / 16) * 16;
+            float2 a2[R], t2[SV_GROUP / 2][R];
+            float2 c_pending = make_float2(0.f, 0.f);         // coefficients of the pair-1 exponents waiting in t2[1]
+#pragma unroll
+            for (int r = 0; r < R; ++r) { a2[r] = make_float2(0.f, 0.f); t2[0][r] = t2[1][r] = make_float2(0.f, 0.f); }
+            auto flush = [&]() {
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    acc64[r] += (double)(a2[r].x + a2[r].y);
+                    a2[r] = make_float2(0.f, 0.f);
+                }
+            };
+#pragma unroll 1
+            for (int q = 0; q < P.sv_quads; ++q) {
+                float2 p2[SV_GROUP / 2][R];
+#pragma unroll
+                for (int st = 0; st < SV_PREFIX; ++st) {
+                    ring[(st + 2) % 3] = tab[st + 2];
+                    const float4 w4 = ring[st % 3];
+                    const float2 wp[SV_GROUP / 2] = {make_float2(w4.x, w4.y), make_float2(w4.z, w4.w)};
+#pragma unroll
+                    for (int h = 0; h < SV_GROUP / 2; ++h)
+#pragma unroll
+                        for (int rr = 0; rr < R; ++rr) {
+                            const int r = (h & 1) ? R - 1 - rr : rr;
+                            const float2 zb = make_float2(zs[st][r], zs[st][r]);
+                            p2[h][r] = st == 0 ? __fmul2_rn(wp[h], zb) : __ffma2_rn(wp[h], zb, p2[h][r]);
+                        }
+                }
+                tab += SV_PREFIX;
+#pragma unroll 1
+                for (int c = quad_steps[q]; c > 0; --c) {
+                    ring[2] = tab[2];
+                    const float4 cq = ring[0];                // this step's folded coefficients: pair 0 .xy, pair 1 .zw
+                    const float2 c_now = make_float2(cq.x, cq.y);
+#pragma unroll
+                    for (int ph = 0; ph < 2; ++ph) {          // phase A: chains of pair 0; phase B: chains of pair 1
+                        const float2 c_ex = ph == 0 ? c_pending : c_now;     // coefficients of the exponents in t2[1 - ph]
+#pragma unroll
+                        for (int j = 0; j < R; ++j) {
+                            const int st = 1 + ph * R + j;
+                            ring[(st + 2) % 3] = tab[st + 2];
+                            const float4 w4 = ring[st % 3];
+                            const float2 wa = make_float2(w4.x, w4.y), wb = make_float2(w4.z, w4.w);
+                            const int fa = SV_PREFIX + 2 * j, fb = fa + 1;
+#pragma unroll
+                            for (int r = 0; r < R; ++r)
+                                t2[ph][r] = __ffma2_rn(wa, make_float2(zs[fa][r], zs[fa][r]), j == 0 ? p2[ph][r] : t2[ph][r]);
+                            t2[1 - ph][j].x = ex2_approx(t2[1 - ph][j].x);
+                            t2[1 - ph][j].y = ex2_approx(t2[1 - ph][j].y);
+#pragma unroll
+                            for (int r = 0; r < R; ++r)      // same row order: dependent FMAs stay 4 instructions apart
+                                t2[ph][r] = __ffma2_rn(wb, make_float2(zs[fb][r], zs[fb][r]), t2[ph][r]);
+                            if (j > 0) a2[j - 1] = __ffma2_rn(t2[1 - ph][j - 1], c_ex, a2[j - 1]);
+                        }
+                        a2[R - 1] = __ffma2_rn(t2[1 - ph][R - 1], c_ex, a2[R - 1]);
+                        // after phase A, a2 holds the four vectors of the previous leaf step: float32 partial sums never
+                        // span more than one step (HFE_PFX_FLUSH 2: two steps) before they go to the float64 accumulator
+                        if (ph == 0 && (HFE_PFX_FLUSH == 1 || (HFE_PFX_FLUSH == 2 && (c & 1)))) flush();
+                    }
+                    c_pending = make_float2(cq.z, cq.w);
+                    tab += SV_LEAF_STEPS;
+                }
+            }
+            // drain: the last step's pair-1 exponents
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                t2[1][r].x = ex2_approx(t2[1][r].x);
+                t2[1][r].y = ex2_approx(t2[1][r].y);
+                a2[r] = __ffma2_rn(t2[1][r], c_pending, a2[r]);
+            }
+            flush();
+        } else
 #pragma unroll 1
         for (int g = 0; g < P.n_groups; ++g) {
             float2 t2[SV_GROUP / 2][R];                   // [support-vector pair][row]
@@ -752,7 +843,7 @@ hfe_apply_kernel(const __grid_constant__ ScoreParams P, unsigned short* leaves) 
     if (row >= P.n) return;
     float xr[F];
 #pragma unroll
-    for (int f = 0; f < F; ++f) xr[f] = __ldg(P.x + (long long)f * P.ld + row);
+    for (int f = 0; f < F; ++f) xr[f] = __ldg(P.x + P.col_off[f] + row);
     for (int t = 0; t < P.n_trees; ++t) {
         int leaf = walk_tree(P, t, [&](unsigned f) {
             float v = xr[0];

@@ -21,6 +21,7 @@
 #include <cmath>
 #include <cstdint>
 #include <cstring>
+#include <functional>
 #include <map>
 #include <mutex>
 #include <string>
@@ -37,6 +38,11 @@ constexpr int MAX_SPLITS = 128;       // merged stump table capacity (kernel par
 constexpr int SV_GROUP = 4;           // support vectors per inner tile
 constexpr int SV_STEPS = F + 1;       // float4 steps per group: F weight steps + one folded-coefficient step
 constexpr int SV_PAD_ROWS = 2;        // zero steps after the table so the 2-step-ahead prefetch may over-read
+constexpr int SV_PREFIX = 9;          // prefix-shared layout: leading (re-ordered) features whose partial exponent is
+                                      // computed once per prefix quad and shared by the support vectors below it
+constexpr int SV_LEAF_STEPS = F - SV_PREFIX + 1;   // per leaf step: the remaining weights + the folded coefficients
+static_assert(SV_PREFIX % 3 == 0 && SV_LEAF_STEPS % 3 == 0 && SV_STEPS % 3 == 0, "3-deep prefetch ring phase");
+static_assert((F - SV_PREFIX) % 2 == 0, "leaf steps hold two features per float4");
 constexpr int SMALL_HOST_ROWS = 4096;   // host batches up to this size use the model's preallocated staging arena
 constexpr int MAX_EDGES = 16;          // coupling-solver discontinuities (6 exist for eps = 0.0025)
 #ifndef HFE_SV_CHUNK
@@ -52,6 +58,8 @@ struct ScoreParams {
     // request
     const float* x;
     long long n, ld;
+    long long col_off[F];       // element offset of internal feature f's column in x: (caller's column) * ld -- the
+                                // model re-orders features (build_model); set per call
     const int* perm_idx;
     int perm_col;
     int n_members;
@@ -69,6 +77,8 @@ struct ScoreParams {
     const double* dual64;       // [n_sv]
     int n_groups;               // multiple of SV_CHUNK / SV_GROUP
     int n_sv;
+    int sv_quads;               // > 0: prefix-shared layout (build_svc), else the flat [n_groups][SV_STEPS] layout
+    int sv_bytes;               // bytes staged in shared memory: table + pad steps (+ the per-quad step counts)
     double mean[F], scale[F];
     float mean_hi[F], mean_lo[F], inv_scale32[F];   // mean = hi + lo in float32; 1/scale rounded once
     double c_log2;              // gamma * log2(e)
@@ -110,6 +120,9 @@ struct Model {
     int n_members = 0;
     int kinds[MAX_MEMBERS] = {0, 0, 0, 0};
     int n_sv = 0, n_trees = 0, n_nodes = 0, max_depth = 0, tree_mode = 0, n_splits = 0;
+    int sv_steps = 0;             // prefix-shared layout: leaf steps (4 support-vector lanes each); 0 = flat layout
+    int col_of[F];                // caller's column of internal feature f
+    int internal_of[F];           // internal feature of caller's column c
     double svc_guard = 0.0;       // assumed |error| of the float32 SVC decision value
     double gbt_guard = 0.0;       // assumed |error| of the float32 boosted raw score
     ScoreParams base{};           // request fields zero; table pointers filled
@@ -341,6 +354,112 @@ inline int build_svc(Model* m, const ParsedBlob& pb, uint32_t idx) {
     // assumed uncertainty of the float32 decision value (DESIGN.md "error budget"): ~20 sigma of the measured error
     m->svc_guard = 3.5e-7 * std::sqrt(coef_l2) + 1e-7;
     P.n_groups = n_groups;
+    P.sv_quads = 0;
+    P.sv_bytes = (int)(tab.size() * sizeof(float4));
+
+    // ---- prefix-shared layout -------------------------------------------------------------------------------------
+    // Support vectors are training rows, and most cohort features are binary, so many vectors agree on their first
+    // SV_PREFIX (re-ordered) features.  The partial exponent over those features is then computed once per distinct
+    // prefix and continued by each vector below it: the same FMA chain as the flat layout, feature by feature, so the
+    // float32 result is the one the flat loop would give for this feature order.  The four SIMD lanes of a table step
+    // walk four independent (prefix, vectors) chunks in lock step; a "quad" is four chunks, its step count the longest
+    // of them, shorter lanes are padded with zero-weight, zero-coefficient vectors.  Large prefix classes are split
+    // into chunks of at most T vectors (the prefix is then recomputed per chunk); T minimises a two-pipe cost model.
+    if (n_sv <= 65536) {
+        std::vector<int> idx(n_sv);
+        for (int j = 0; j < n_sv; ++j) idx[j] = j;
+        auto prefix_less = [&](int a, int b) {
+            const double* sa = sv->f64() + (size_t)a * F;
+            const double* sb = sv->f64() + (size_t)b * F;
+            for (int d = 0; d < SV_PREFIX; ++d)
+                if (sa[d] != sb[d]) return sa[d] < sb[d];
+            return false;
+        };
+        std::stable_sort(idx.begin(), idx.end(), prefix_less);
+        std::vector<std::pair<int, int>> classes;          // (first position in idx, size)
+        for (int k = 0; k < n_sv; ++k) {
+            if (k == 0 || prefix_less(idx[k - 1], idx[k])) classes.push_back({k, 1});
+            else classes.back().second++;
+        }
+        auto pipe_cost = [](double fma_lane_ops, double xu_ops) {
+            double a = fma_lane_ops / 128.0, b = xu_ops / 16.0;       // clocks per row on the FMA and MUFU pipes of one SM
+            return std::max(a, b) + 0.3 * std::min(a, b);
+        };
+        auto split_sizes = [&](int T, std::vector<int>* sizes) {
+            sizes->clear();
+            for (auto& c : classes) {
+                int parts = (c.second + T - 1) / T, base = c.second / parts, extra = c.second % parts;
+                for (int i = 0; i < parts; ++i) sizes->push_back(base + (i < extra ? 1 : 0));
+            }
+            std::sort(sizes->begin(), sizes->end(), std::greater<int>());
+        };
+        int largest = 0;
+        for (auto& c : classes) largest = std::max(largest, c.second);
+        int best_T = 0;
+        double best_cost = 0;
+        std::vector<int> sizes;
+        for (int T = 1; T <= std::min(largest, 255); ++T) {
+            split_sizes(T, &sizes);
+            long long quads = ((long long)sizes.size() + 3) / 4, steps = 0;
+            for (size_t q = 0; q < sizes.size(); q += 4) steps += sizes[q];
+            double cost = pipe_cost(4.0 * (quads * SV_PREFIX + steps * SV_LEAF_STEPS), 5.0 * steps);
+            if (best_T == 0 || cost < best_cost) { best_T = T; best_cost = cost; }
+        }
+        double flat_cost = pipe_cost(4.0 * n_groups * SV_STEPS, 5.0 * n_groups);
+        if (best_T > 0 && best_cost < 0.9 * flat_cost) {
+            struct Chunk { int first, count; };
+            std::vector<Chunk> chunks;
+            for (auto& c : classes) {
+                int parts = (c.second + best_T - 1) / best_T, base = c.second / parts, extra = c.second % parts, at = c.first;
+                for (int i = 0; i < parts; ++i) {
+                    int cnt = base + (i < extra ? 1 : 0);
+                    chunks.push_back({at, cnt});
+                    at += cnt;
+                }
+            }
+            std::stable_sort(chunks.begin(), chunks.end(), [](const Chunk& a, const Chunk& b) { return a.count > b.count; });
+            int quads = ((int)chunks.size() + 3) / 4;
+            long long steps = 0;
+            for (size_t q = 0; q < chunks.size(); q += 4) steps += chunks[q].count;
+            size_t slots = (size_t)quads * SV_PREFIX + (size_t)steps * SV_LEAF_STEPS;
+            size_t count_slots = ((size_t)quads + 15) / 16;
+            std::vector<float4> ptab(slots + SV_PAD_ROWS + count_slots, make_float4(0.f, 0.f, 0.f, 0.f));
+            unsigned char* counts = reinterpret_cast<unsigned char*>(&ptab[slots + SV_PAD_ROWS]);
+            size_t at = 0;
+            for (int q = 0; q < quads; ++q) {
+                int qsteps = chunks[(size_t)q * 4].count;
+                counts[q] = (unsigned char)qsteps;
+                float* pre = reinterpret_cast<float*>(&ptab[at]);
+                float* leaf = reinterpret_cast<float*>(&ptab[at + SV_PREFIX]);
+                for (int lane = 0; lane < 4; ++lane) {
+                    size_t ci = (size_t)q * 4 + lane;
+                    if (ci >= chunks.size()) continue;                       // whole lane stays zero
+                    const double* s0 = sv->f64() + (size_t)idx[chunks[ci].first] * F;
+                    for (int d = 0; d < SV_PREFIX; ++d) pre[d * 4 + lane] = (float)(2.0 * P.c_log2 * s0[d]);
+                    for (int k = 0; k < chunks[ci].count; ++k) {
+                        int j = idx[chunks[ci].first + k];
+                        const double* s = sv->f64() + (size_t)j * F;
+                        double ss = 0;
+                        for (int d = 0; d < F; ++d) ss += s[d] * s[d];
+                        // leaf step: [coefficients of the 4 lanes][pair 0 (lanes 0,1): 4 float4, each two features x two
+                        // lanes][pair 1 (lanes 2,3): the same]
+                        float* step = leaf + (size_t)k * SV_LEAF_STEPS * 4;
+                        step[lane] = (float)(coef[j] * std::exp2(-P.c_log2 * ss));
+                        float* pair = step + 4 + (lane / 2) * ((F - SV_PREFIX) / 2) * 4;
+                        for (int d = SV_PREFIX; d < F; ++d) {
+                            int e = d - SV_PREFIX;
+                            pair[(e / 2) * 4 + (e % 2) * 2 + (lane % 2)] = (float)(2.0 * P.c_log2 * s[d]);
+                        }
+                    }
+                }
+                at += SV_PREFIX + (size_t)qsteps * SV_LEAF_STEPS;
+            }
+            tab.swap(ptab);
+            P.sv_quads = quads;
+            P.sv_bytes = (int)(tab.size() * sizeof(float4));
+            m->sv_steps = (int)steps;
+        }
+    }
     std::vector<double> sv_host(sv->f64(), sv->f64() + (size_t)n_sv * F), dual_host(coef, coef + n_sv);
     int rc;
     if ((rc = upload(m, tab, &P.sv_tab))) return rc;
@@ -498,10 +617,90 @@ inline int build_gbt(Model* m, const ParsedBlob& pb, uint32_t idx) {
     return HFE_OK;
 }
 
+// ---- internal feature order --------------------------------------------------------------------------------------------
+// The prefix-shared support-vector layout (build_svc) pays off when many vectors agree on their leading features, so the
+// model is rebuilt in a feature order that puts the columns with the fewest distinct prefixes first (greedy, one column
+// at a time).  Every per-feature table of every member is permuted the same way before the members are built; the
+// kernels read caller column ScoreParams::col[f] for internal feature f, so nothing changes at the C boundary.
+inline void choose_feature_order(const double* sv, int n_sv, int order[F]) {
+    bool used[F] = {};
+    std::vector<int> cls(n_sv, 0);
+    std::vector<std::pair<std::pair<int, double>, int>> keys(n_sv);
+    auto refine = [&](int col, bool assign) -> size_t {
+        for (int j = 0; j < n_sv; ++j) keys[j] = {{cls[j], sv[(size_t)j * F + col] + 0.0}, j};
+        std::sort(keys.begin(), keys.end());
+        size_t distinct = 0;
+        for (int k = 0; k < n_sv; ++k) {
+            if (k == 0 || keys[k].first != keys[k - 1].first) ++distinct;
+            if (assign) cls[keys[k].second] = (int)distinct - 1;
+        }
+        return distinct;
+    };
+    for (int pos = 0; pos < F; ++pos) {
+        int best = -1;
+        size_t best_count = 0;
+        for (int c = 0; c < F; ++c) {
+            if (used[c]) continue;
+            if (pos >= SV_PREFIX) { best = c; break; }               // beyond the prefix the order does not matter
+            size_t count = refine(c, false);
+            if (best < 0 || count < best_count) { best = c; best_count = count; }
+        }
+        used[best] = true;
+        order[pos] = best;
+        if (pos < SV_PREFIX) refine(best, true);
+    }
+}
+
+// Copies of the per-feature blob sections in internal feature order (ParsedBlob sections otherwise point into the
+// caller's blob).  Sections that are missing or mis-sized are left alone: the member builders report them.
+inline void permute_sections(ParsedBlob* pb, const int order[F], std::vector<std::vector<uint8_t>>* owned) {
+    int internal_of[F];
+    for (int f = 0; f < F; ++f) internal_of[order[f]] = f;
+    auto own = [&](Section* s, size_t bytes) -> uint8_t* {
+        owned->emplace_back(s->data, s->data + bytes);
+        s->data = owned->back().data();
+        return owned->back().data();
+    };
+    for (auto& kv : pb->sections) {
+        uint32_t kind = kv.first.first;
+        Section& s = kv.second;
+        if ((kind == K_SVC_MEAN || kind == K_SVC_SCALE || kind == K_SVC_SV) && s.count >= (uint64_t)F && s.count % F == 0) {
+            std::vector<double> src(s.f64(), s.f64() + s.count);
+            double* dst = reinterpret_cast<double*>(own(&s, s.count * 8));
+            for (uint64_t r = 0; r < s.count / F; ++r)
+                for (int f = 0; f < F; ++f) dst[r * F + f] = src[r * F + order[f]];
+        } else if (kind == K_LIN_PARAMS && s.count == (uint64_t)F + 1) {
+            std::vector<double> src(s.f64(), s.f64() + s.count);
+            double* dst = reinterpret_cast<double*>(own(&s, s.count * 8));
+            for (int f = 0; f < F; ++f) dst[f] = src[order[f]];
+        } else if (kind == K_GBT_FEATURE) {
+            int32_t* dst = reinterpret_cast<int32_t*>(own(&s, s.count * 4));
+            for (uint64_t i = 0; i < s.count; ++i)
+                if (dst[i] >= 0 && dst[i] < F) dst[i] = internal_of[dst[i]];
+        }
+    }
+}
+
 inline int build_model(const uint8_t* blob, size_t len, int device, Model** out) {
     ParsedBlob pb;
     int rc = parse_blob(blob, len, &pb);
     if (rc) return rc;
+    int order[F];
+    for (int f = 0; f < F; ++f) order[f] = f;
+    std::vector<std::vector<uint8_t>> owned_sections;
+    if (pb.n_features == (uint32_t)F) {
+        for (uint32_t i = 0; i < pb.n_members && i < (uint32_t)MAX_MEMBERS; ++i) {
+            const Section* ps = pb.find(K_SVC_PARAMS, i, 8);
+            if (!ps) continue;
+            double n_sv_d = ps->f64()[4];
+            if (!(n_sv_d >= 1 && n_sv_d <= 65536) || n_sv_d != std::floor(n_sv_d)) break;
+            const Section* sv = pb.find(K_SVC_SV, i, (uint64_t)n_sv_d * F);
+            if (!sv || !all_finite(sv->f64(), sv->count)) break;
+            choose_feature_order(sv->f64(), (int)n_sv_d, order);
+            permute_sections(&pb, order, &owned_sections);
+            break;
+        }
+    }
     if (pb.n_features != (uint32_t)F)
         return fail(HFE_ERR_UNSUPPORTED, "this build scores the 17-feature schema only (HFE_N_FEATURES)");
     if (pb.n_members > (uint32_t)MAX_MEMBERS) return fail(HFE_ERR_UNSUPPORTED, "more than 4 stack members");
@@ -518,6 +717,10 @@ inline int build_model(const uint8_t* blob, size_t len, int device, Model** out)
     P.slot_svc = P.slot_gbt = P.slot_lin = -1;
     P.n_members = m->n_members;
     P.perm_col = -1;
+    for (int f = 0; f < F; ++f) {
+        m->col_of[f] = order[f];
+        m->internal_of[order[f]] = f;
+    }
     for (uint32_t i = 0; i < pb.n_members && rc == HFE_OK; ++i) {
         P.final_coef[i] = fin->f64()[i];
         if (pb.has(K_SVC_PARAMS, i)) {

@@ -395,8 +395,68 @@ def test_large_support_vector_tables(pkg, published, torch_cuda):
     assert np.array_equal(clf.predict(X), so.predict(arrays, X))
     clf.close()
     too_big = pkg.HFStackB200.from_arrays(with_svs(1600))
-    with pytest.raises(pkg.capi.HfeError, match="support vectors"):
+    with pytest.raises(pkg.capi.HfeError, match="support-vector table"):
         too_big.predict_proba(X[:8])
+
+
+def test_prefix_shared_support_vector_layout(pkg, published, retrained, torch_cuda):
+    """The prefix-shared table layout (shared partial dot products over the re-ordered leading features): in use for
+    both fixture models, falls back to the flat layout when support vectors share nothing, and stays within the
+    parity bars on degenerate tables (one vector; every vector sharing one prefix; all-binary vectors with many
+    duplicates of a prefix) -- which also exercises the internal feature re-ordering of every member."""
+    import copy
+    rng = np.random.default_rng(23)
+    for fx in (published, retrained):
+        clf = pkg.HFStackB200.from_arrays(fx["arrays"])
+        n_sv = int(clf.info.n_support_vectors)
+        flat = (n_sv + 3) // 4 * 4 * 18
+        assert 0 < clf.info.rbf_fma_per_row < 0.75 * flat
+        clf.close()
+
+    base = published["arrays"]
+    X = pkg.synth.host_rows(published["specs"], 29, 0, 5000).astype(np.float64)
+
+    def variant(make_sv, n_sv):
+        arrays = copy.deepcopy(base)
+        svc = arrays.members[0]
+        pick = rng.integers(0, svc.sv.shape[0], n_sv)
+        svc.sv = make_sv(svc.sv[pick].copy())
+        svc.dual_coef = svc.dual_coef[pick] * min(434.0 / n_sv, 4.0)
+        order = np.argsort(svc.dual_coef > 0, kind="stable")
+        svc.sv, svc.dual_coef = svc.sv[order], svc.dual_coef[order]
+        n0 = int((svc.dual_coef <= 0).sum())
+        svc.n_support = np.array([n0, n_sv - n0])
+        return arrays
+
+    def continuous(sv):                      # nothing shared: flat layout
+        return sv + rng.normal(0, 0.05, sv.shape)
+
+    def one_prefix(sv):                      # every vector agrees on 13 columns: one class, split into chunks
+        sv[:, :13] = sv[0, :13]
+        sv[:, 13:] += rng.normal(0, 0.3, sv[:, 13:].shape)
+        return sv
+
+    def all_binary(sv):                      # few distinct rows, many exact duplicates
+        lo, hi = base.members[0].sv.min(axis=0), base.members[0].sv.max(axis=0)
+        bits = rng.integers(0, 2, (6, 17))
+        return np.where(bits[rng.integers(0, 6, len(sv))] == 1, hi, lo)
+
+    cases = [(continuous, 200, False), (one_prefix, 57, True), (all_binary, 131, True), (lambda sv: sv, 1, None),
+             (lambda sv: sv, 3, None)]
+    for make_sv, n_sv, expect_shared in cases:
+        arrays = variant(make_sv, n_sv)
+        clf = pkg.HFStackB200.from_arrays(arrays)
+        flat = (n_sv + 3) // 4 * 4 * 18
+        if expect_shared is True:
+            assert clf.info.rbf_fma_per_row < flat
+        elif expect_shared is False:
+            assert clf.info.rbf_fma_per_row == flat
+        assert np.abs(clf.predict_proba(X) - so.predict_proba(arrays, X)).max() <= PROBA_TOL
+        assert np.array_equal(clf.predict(X), so.predict(arrays, X))
+        assert np.abs(clf.transform(X) - so.transform(arrays, X)).max() <= PROBA_TOL
+        gbt = [m for m in arrays.members if m.kind == "gbt"][0]
+        assert np.array_equal(clf.apply(X[:500]), so.gbt_apply(gbt, X[:500]))
+        clf.close()
 
 
 def test_bounds_checked_build_on_small_and_ragged_cases(cuda_lib):
