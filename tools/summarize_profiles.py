@@ -81,9 +81,10 @@ def full(rep, tag, title, n_rows, write_traffic):
     hot = [i for i, e in enumerate(ex) if e >= max(ex) * 0.9]
     tot = sum(samples)
     if len(hot) > 100:
-        out += [f"Warp-state samples: RBF loop ({len(hot)} SASS instructions per 4 support vectors) "
+        out += [f"Warp-state samples: RBF leaf loop ({len(hot)} SASS instructions per 4 support vectors) "
                 f"{100 * sum(samples[i] for i in hot) / tot:.1f} %, before it {100 * sum(samples[:hot[0]]) / tot:.1f} %, "
-                f"after it {100 * sum(samples[hot[-1] + 1:]) / tot:.1f} %.", ""]
+                f"after it {100 * sum(samples[hot[-1] + 1:]) / tot:.1f} % (with the prefix-shared table layout the "
+                f"prefix-quad steps, executed once per quad, count as 'before').", ""]
     open(os.path.join(OUT, f"r1_{tag}_kernel.md"), "w").write("\n".join(out) + "\n")
 
 
@@ -94,7 +95,7 @@ if __name__ == "__main__":
     full("prof_r1_nosvc.ncu-rep", "nosvc", "fused kernel `hfe_score_kernel<no SVC, stumps>` (the HBM-bound configuration)",
          10_000_000, False)
     for name in ("retrained", "published", "nosvc", "stress", "reference"):
-        p = os.path.join(SRC, f"bench_{name}.json")
+        p = os.path.join(SRC, f"r1_bench_{name}.json")
         if os.path.exists(p):
             open(os.path.join(OUT, f"r1_bench_{name}.json"), "w").write(open(p).read().strip().splitlines()[-1] + "\n")
     for name in ("scale2", "scale8", "scale8_1b", "scale8_stress", "perm8"):
