@@ -127,6 +127,17 @@ int hfe_ingest_rowmajor_f64(const double* x_rowmajor, int64_t n, int32_t n_featu
 int hfe_ingest_rowmajor_f32(const float* x_rowmajor, int64_t n, int32_t n_features, float* x, int64_t ld,
                             uint32_t* status, void* stream);
 
+/* Same for the int64 matrix predict_hf.py:29-36 builds (a Python list of ints through np.array): each value goes
+ * through float64 to float32, as scikit-learn's validate_data followed by the float32 cast does. */
+int hfe_ingest_rowmajor_i64(const int64_t* x_rowmajor, int64_t n, int32_t n_features, float* x, int64_t ld,
+                            uint32_t* status, void* stream);
+/* Same for a cohort stored as unsigned bytes.  No counterpart in the reference: every variable of the
+ * load_data_public.py schema is a small non-negative integer (13 yes/no flags, NYHA class, wall thickness in mm,
+ * SAM / regurgitation grade, ejection fraction in %), so a large cohort can be kept and shipped to the GPU at 17 bytes
+ * per patient instead of 68 -- the host-to-device copy is what bounds end-to-end throughput. */
+int hfe_ingest_rowmajor_u8(const uint8_t* x_rowmajor, int64_t n, int32_t n_features, float* x, int64_t ld,
+                           uint32_t* status, void* stream);
+
 /* The evaluation train_ensemble_public.py:63-64,67,79 performs next on the probabilities (classification_report of
  * ``y_pred[:,1] > 0.5``, ROC and precision-recall curves): confusion[0..3] = tn, fp, fn, tp at `threshold` (uint64,
  * zeroed by the call); hist (may be NULL) = 2 x HFE_METRIC_BINS uint32, per true class the histogram of P(class 1) in

@@ -284,6 +284,16 @@ int hfe_ingest_rowmajor_f32(const float* x_rowmajor, int64_t n, int32_t n_featur
     return ingest_common(x_rowmajor, n, n_features, x, ld, status, stream);
 }
 
+int hfe_ingest_rowmajor_i64(const int64_t* x_rowmajor, int64_t n, int32_t n_features, float* x, int64_t ld,
+                            uint32_t* status, void* stream) {
+    return ingest_common(reinterpret_cast<const long long*>(x_rowmajor), n, n_features, x, ld, status, stream);
+}
+
+int hfe_ingest_rowmajor_u8(const uint8_t* x_rowmajor, int64_t n, int32_t n_features, float* x, int64_t ld,
+                           uint32_t* status, void* stream) {
+    return ingest_common(x_rowmajor, n, n_features, x, ld, status, stream);
+}
+
 int hfe_binary_metrics(const float* proba_n2, const uint8_t* y, int64_t n, float threshold,
                        unsigned long long* confusion, uint32_t* hist, void* stream) {
     if (n < 0 || !confusion) return fail(HFE_ERR_INVALID_ARGUMENT, "bad metrics arguments");

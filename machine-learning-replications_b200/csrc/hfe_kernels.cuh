@@ -294,6 +294,26 @@ __device__ __forceinline__ float4 fix_rows4(const ScoreParams& P, int f, long lo
     return v;
 }
 
+// Merged depth-1 stumps of feature f (compile-time index): the first split of every feature sits in the parameter
+// block as immediate constant operands (threshold -inf, delta 0 where a feature has none), further splits of the same
+// feature in a table behind it.
+template <int R>
+__device__ __forceinline__ void apply_splits(const ScoreParams& P, int f, const float (&x)[R], float (&acc)[R]) {
+    const float thr0 = P.split1_thr[f], dl0 = P.split1_delta[f];
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+        if (x[r] <= thr0) acc[r] += dl0;
+    if (P.split_begin[f + 1] != P.split_begin[f]) {
+#pragma unroll 1
+        for (int s = P.split_begin[f]; s < P.split_begin[f + 1]; ++s) {
+            const float thr = P.split_thr[s], dl = P.split_delta[s];
+#pragma unroll
+            for (int r = 0; r < R; ++r)
+                if (x[r] <= thr) acc[r] += dl;
+        }
+    }
+}
+
 // Walk one tree for one row: x values come from `xrow` (F floats, any address space).  Returns the re-laid leaf index
 // (global node index).
 template <typename XGet>
@@ -458,15 +478,7 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int sv_bytes) {
                 else finite_probe = fmaf(xf[r], 0.f, finite_probe);
                 if (TREE_MODE == 2) s_xt[f * BLOCK_ROWS + r * BLOCK_THREADS + tid] = xf[r];
             }
-            if (TREE_MODE == 1) {
-#pragma unroll 1
-    #pragma unroll 1
-            for (int s = P.split_begin[f]; s < P.split_begin[f + 1]; ++s) {
-                    float thr = P.split_thr[s], dl = P.split_delta[s];
-#pragma unroll
-                    for (int r = 0; r < R; ++r) acc[r] += (xf[r] <= thr) ? dl : 0.f;
-                }
-            }
+            if (TREE_MODE == 1) apply_splits<R>(P, f, xf, acc);
         }
         nonfinite = !(finite_probe == 0.f);
         if (has_lin) {
@@ -512,14 +524,7 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int sv_bytes) {
 #pragma unroll
         for (int r = 0; r < R; ++r) acc[r] = 0.f;
 #pragma unroll
-        for (int f = 0; f < F; ++f) {
-#pragma unroll 1
-            for (int s = P.split_begin[f]; s < P.split_begin[f + 1]; ++s) {
-                float thr = P.split_thr[s], dl = P.split_delta[s];
-#pragma unroll
-                for (int r = 0; r < R; ++r) acc[r] += (xv[f][r] <= thr) ? dl : 0.f;
-            }
-        }
+        for (int f = 0; f < F; ++f) apply_splits<R>(P, f, xv[f], acc);
 #pragma unroll
         for (int r = 0; r < R; ++r) raw[r] = P.gbt_split_base + (double)acc[r];
     }
@@ -895,7 +900,7 @@ hfe_ingest_kernel(const T* __restrict__ src, long long n, int nf, float* __restr
     bool bad = false;
     for (int i = threadIdx.x; i < rows * nf; i += BLOCK_THREADS) {
         T v = src[r0 * nf + i];
-        float fv = (float)v;                       // round-to-nearest, like numpy's astype(float32)
+        float fv = (float)(double)v;               // via float64, like validate_data + astype(float32) (matters for int64)
         bad = bad || !(fabsf(fv) <= 3.402823466e38f);   // NaN/Inf, or a float64 too large for float32
         s_tile[(i / nf) * pitch + (i % nf)] = fv;
     }

@@ -94,7 +94,8 @@ struct ScoreParams {
     int n_splits;
     double gbt_init;            // init raw prediction
     double gbt_split_base;      // init + sum of right-leaf values (merged stump mode)
-    int split_begin[F + 1];
+    float split1_thr[F], split1_delta[F];   // first merged split of each feature (-inf / 0 where there is none)
+    int split_begin[F + 1];                 // the remaining splits of feature f: [split_begin[f], split_begin[f+1])
     float split_thr[MAX_SPLITS];
     float split_delta[MAX_SPLITS];
     const uint2* nodes;         // {thr32 bits, feature<<24 | child}: child = GLOBAL index of the left child (right = +1)
@@ -591,19 +592,27 @@ inline int build_gbt(Model* m, const ParsedBlob& pb, uint32_t idx) {
     if (all_stumps && (int)merged.size() <= MAX_SPLITS) {
         m->tree_mode = 1;
         int s = 0, f_cur = 0;
+        bool have_first[F] = {};
+        for (int f = 0; f < F; ++f) { P.split1_thr[f] = -INFINITY; P.split1_delta[f] = 0.f; }
         P.split_begin[0] = 0;
         for (auto& kv : merged) {               // std::map iterates sorted by (feature, bits)
             while (f_cur < kv.first.first) P.split_begin[++f_cur] = s;
             float t32;
             std::memcpy(&t32, &kv.first.second, 4);
+            if (!have_first[kv.first.first]) {
+                have_first[kv.first.first] = true;
+                P.split1_thr[kv.first.first] = t32;
+                P.split1_delta[kv.first.first] = (float)kv.second;
+                continue;
+            }
             P.split_thr[s] = t32;
             P.split_delta[s] = (float)kv.second;
             ++s;
         }
         while (f_cur < F) P.split_begin[++f_cur] = s;
-        P.n_splits = s;
+        P.n_splits = (int)merged.size();
         P.gbt_split_base = init_raw + right_sum;
-        m->n_splits = s;
+        m->n_splits = (int)merged.size();
     } else {
         m->tree_mode = 2;
     }

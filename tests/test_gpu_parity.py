@@ -459,6 +459,30 @@ def test_prefix_shared_support_vector_layout(pkg, published, retrained, torch_cu
         clf.close()
 
 
+def test_integer_cohort_ingest(pkg, published, torch_cuda):
+    """int64 (what predict_hf.py:29-36 passes) and uint8 cohort matrices through the device ingest kernels give the
+    bytes the float64 route gives; the pinned pipeline accepts them too."""
+    import torch
+    clf = pkg.HFStackB200.from_arrays(published["arrays"])
+    X = pkg.synth.host_rows(published["specs"], 31, 0, 4099)
+    assert np.all(X == np.round(X)) and X.min() >= 0 and X.max() <= 255
+    want = clf.to_device_colmajor(X.astype(np.float64))
+    for dt in (np.int64, np.uint8, np.float32, np.int32):
+        got = clf.to_device_colmajor(X.astype(dt))
+        assert torch.equal(got, want), dt
+    ref = clf.predict_proba(X.astype(np.float64))
+    for tdt in (torch.int64, torch.uint8):
+        xh = torch.from_numpy(X).to(tdt).pin_memory()
+        out = clf.predict_proba_pinned(xh, chunk_rows=1024)
+        assert np.abs(out.numpy().astype(np.float64) - ref).max() <= 1e-7
+    big = np.array([[2 ** 40 + 1] * 17], dtype=np.int64)                  # int64 -> float64 -> float32, like numpy
+    got = clf.to_device_colmajor(big)[:, 0].cpu().numpy()
+    assert np.array_equal(got, big[0].astype(np.float64).astype(np.float32))
+    with pytest.raises(ValueError):
+        clf.predict_proba_pinned(torch.zeros((8, 17), dtype=torch.int16).pin_memory())
+    clf.close()
+
+
 def test_bounds_checked_build_on_small_and_ragged_cases(cuda_lib):
     """Every kernel at tiny / ragged sizes against the library built with -DHFE_BOUNDS_CHECK: any access outside the
     declared extents of x, perm_idx or the outputs traps and the run fails (stands in for compute-sanitizer)."""
