@@ -441,8 +441,23 @@ def test_prefix_shared_support_vector_layout(pkg, published, retrained, torch_cu
         bits = rng.integers(0, 2, (6, 17))
         return np.where(bits[rng.integers(0, 6, len(sv))] == 1, hi, lo)
 
+    def mixture(n_binary, n_levels):
+        """n_binary two-valued columns (random positions), the rest with n_levels distinct values."""
+        def make(sv):
+            lo, hi = base.members[0].sv.min(axis=0), base.members[0].sv.max(axis=0)
+            cols = rng.permutation(17)
+            out = np.empty_like(sv)
+            for k, c in enumerate(cols):
+                levels = 2 if k < n_binary else n_levels
+                grid = np.linspace(lo[c], hi[c], levels)
+                out[:, c] = grid[rng.integers(0, levels, len(sv))]
+            return out
+        return make
+
     cases = [(continuous, 200, False), (one_prefix, 57, True), (all_binary, 131, True), (lambda sv: sv, 1, None),
-             (lambda sv: sv, 3, None)]
+             (lambda sv: sv, 3, None), (mixture(17, 2), 300, None), (mixture(12, 5), 900, None),
+             (mixture(9, 30), 433, None), (mixture(5, 3), 64, None), (mixture(14, 200), 7, None),
+             (mixture(10, 4), 1500, None)]
     for make_sv, n_sv, expect_shared in cases:
         arrays = variant(make_sv, n_sv)
         clf = pkg.HFStackB200.from_arrays(arrays)
