@@ -59,8 +59,70 @@ int launch_score(const Model* m, const ScoreParams& P, cudaStream_t stream) {
     return HFE_OK;
 }
 
+// Tensor map of the caller's column-major matrix for the streaming pass: dimension 0 = rows (contiguous, extent n so
+// that the copy engine zero-fills the ragged tail), dimension 1 = the 17 feature columns (stride ld floats), box =
+// one warp tile.  cuTensorMapEncodeTiled is a host-only driver call; it is looked up through the runtime so that the
+// library does not link against libcuda (it must still load on a machine without a driver).
+int make_x_map(const ScoreParams& P, CUtensorMap* map) {
+    typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                 const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static EncodeFn encode = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            encode = reinterpret_cast<EncodeFn>(fn);
+    });
+    if (!encode) return fail(HFE_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
+    const cuuint64_t dims[2] = {(cuuint64_t)P.n, (cuuint64_t)F};
+    const cuuint64_t strides[1] = {(cuuint64_t)P.ld * sizeof(float)};
+    const cuuint32_t box[2] = {(cuuint32_t)WARP_ROWS, (cuuint32_t)F};
+    const cuuint32_t elem[2] = {1, 1};
+    CUresult r = encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(P.x), dims, strides, box, elem,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(HFE_ERR_CUDA, "cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")");
+    return HFE_OK;
+}
+
+template <int TM>
+int launch_stream(const Model* m, const ScoreParams& P, cudaStream_t stream) {
+    CUtensorMap x_map;
+    int rc = make_x_map(P, &x_map);
+    if (rc) return rc;
+    auto kernel = hfe_stream_kernel<TM>;
+    static std::mutex mu;
+    static std::map<int, int> resident;
+    int per_sm = 0, sms = 0;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        auto it = resident.find(m->device);
+        if (it == resident.end()) {
+            HFE_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)STREAM_SMEM_BYTES));
+            HFE_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, BLOCK_THREADS, STREAM_SMEM_BYTES));
+            if (per_sm < 1) return fail(HFE_ERR_UNSUPPORTED, "streaming pass does not fit one SM's shared memory");
+            resident[m->device] = per_sm;
+        } else {
+            per_sm = it->second;
+        }
+    }
+    HFE_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, m->device));
+    long long tiles = (P.n + WARP_ROWS - 1) / WARP_ROWS;
+    long long blocks = std::min<long long>((tiles + BLOCK_WARPS - 1) / BLOCK_WARPS, (long long)sms * per_sm);
+    kernel<<<(unsigned)blocks, BLOCK_THREADS, STREAM_SMEM_BYTES, stream>>>(P, x_map);
+    HFE_CUDA_TRY(cudaGetLastError());
+    return HFE_OK;
+}
+
 int dispatch_score(const Model* m, const ScoreParams& P, cudaStream_t stream) {
     bool svc = P.slot_svc >= 0;
+    bool identity = true;                          // the feature order is only changed for stacks with an SVC member
+    for (int f = 0; f < F; ++f) identity = identity && m->col_of[f] == f;
+    if (HFE_STREAM_TMA && !svc && m->tree_mode != 2 && identity)
+        return m->tree_mode == 0 ? launch_stream<0>(m, P, stream) : launch_stream<1>(m, P, stream);
     if (svc && P.sv_quads > 0) {
         switch (m->tree_mode) {
             case 0: return launch_score<true, 0, true>(m, P, stream);

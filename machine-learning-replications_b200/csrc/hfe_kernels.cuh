@@ -14,6 +14,8 @@
 // collected per block and re-evaluated cooperatively in float64 (eval_row_f64) before the block retires.
 #pragma once
 
+#include <cuda.h>          // CUtensorMap (types only; the encoder is fetched through cudaGetDriverEntryPoint)
+
 #include "hfe_model.cuh"
 
 namespace hfe {
@@ -38,6 +40,12 @@ constexpr int TREE_CHUNK = 16;            // float32 partial sums over trees are
 #endif
 #ifndef HFE_PFX_FLUSH
 #define HFE_PFX_FLUSH 1                   // float32 partial sums go to float64 after every leaf step (1) or every 2nd (2)
+#endif
+#ifndef HFE_MIN_BLOCKS_STREAM
+#define HFE_MIN_BLOCKS_STREAM 5           // streaming pass: register cap; 6 blocks x 4 warps x one 8.5 KB tile stage = 204 KB of shared memory per SM
+#endif
+#ifndef HFE_STREAM_TMA
+#define HFE_STREAM_TMA 1                  // SVC-free stacks with stumps / no trees go through hfe_stream_kernel
 #endif
 #ifndef HFE_MIN_BLOCKS_PFX
 #define HFE_MIN_BLOCKS_PFX 4              // same, for the prefix-shared support-vector layout
@@ -109,6 +117,17 @@ __device__ __forceinline__ double expit_fast(double x) {
     double e = exp_neg_fast(-fabs(x));
     double inv = rcp_fast(1.0 + e);
     return x >= 0 ? inv : e * inv;
+}
+
+// float32 logistic link for the streaming pass: e = 2^(-|x| log2 e) in (0, 1] by MUFU.EX2, 1/(1+e) by MUFU.RCP + one
+// Newton step; |error| <= ~1.8e-7 absolute.
+__device__ __forceinline__ float expit32(float x) {
+    const float e = ex2_approx(-fabsf(x) * 1.4426950408889634f);
+    const float d = 1.f + e;
+    float inv;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(d));
+    inv = fmaf(inv, fmaf(-d, inv, 1.f), inv);
+    return x >= 0.f ? inv : e * inv;
 }
 
 // Links of the members that do not depend on the RBF sum, and their share of the combiner's logit:
@@ -393,6 +412,58 @@ __device__ __noinline__ bool eval_row_f64_warp(const ScoreParams& P, long long r
     }
     label = __shfl_sync(full_mask, label, 0);
     return P.y ? (label == (int)P.y[row]) : false;
+}
+
+// Outputs of one thread's R rows, the work list and the accuracy count -- shared by the fused pass and the streaming pass.
+template <int R, typename T>
+__device__ __forceinline__ void emit_rows(const ScoreParams& P, long long row0, int lane, bool full, bool nonfinite,
+                                          unsigned fixmask, const T (&p1)[R], const T (&zfin)[R],
+                                          const T (&p_svc)[R], const bool (&unc)[R]) {
+    unsigned char lab[R];
+    float po[2 * R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        po[2 * r] = (float)(T(1) - p1[r]);
+        po[2 * r + 1] = (float)p1[r];
+        lab[r] = zfin[r] > 0 ? 1 : 0;
+        if (unc[r]) fixmask |= 1u << r;
+        if (row0 + r >= P.n) continue;
+        if (P.out && !full) { P.out[2 * (row0 + r)] = po[2 * r]; P.out[2 * (row0 + r) + 1] = po[2 * r + 1]; }
+        if (P.out64) { P.out64[2 * (row0 + r)] = (double)(T(1) - p1[r]); P.out64[2 * (row0 + r) + 1] = (double)p1[r]; }
+        if (P.labels) P.labels[row0 + r] = lab[r];
+        if (P.decision) P.decision[row0 + r] = zfin[r];
+        if (P.meta && P.slot_svc >= 0) P.meta[(row0 + r) * P.n_members + P.slot_svc] = p_svc[r];
+    }
+    if (P.out && full) {                        // 4 rows x [p0, p1] = two 128-bit stores, 32 contiguous bytes per thread
+        float4* o = reinterpret_cast<float4*>(P.out + 2 * row0);
+        o[0] = make_float4(po[0], po[1], po[2], po[3]);
+        o[1] = make_float4(po[4], po[5], po[6], po[7]);
+    }
+    if (!full) fixmask &= (1u << (unsigned)max(0LL, min((long long)R, P.n - row0))) - 1u;
+    if (nonfinite) fixmask = full ? (1u << R) - 1 : fixmask | ((1u << (unsigned)max(0LL, min((long long)R, P.n - row0))) - 1u);
+
+    // ---- rows whose result hinges on a branch go to the work list; hfe_fixup_kernel re-evaluates them in float64 -------
+    if (fixmask) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            if ((fixmask >> r) & 1u) {
+                unsigned slot = atomicAdd(P.status + HFE_STATUS_LIST_LEN, 1u);
+                if (slot < (unsigned)HFE_WORKLIST_CAPACITY) P.status[HFE_STATUS_HEADER_WORDS + slot] = (unsigned)(row0 + r);
+                else atomicOr(P.status, HFE_WORKLIST_OVERFLOW);
+            }
+        }
+    }
+    if (nonfinite) atomicOr(P.status, HFE_ROW_NONFINITE);
+
+    if (P.y && P.score) {                                         // accuracy count; flagged rows are counted by the fix-up
+        unsigned hits = 0;
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+            if (row0 + r < P.n && !((fixmask >> r) & 1u)) hits += (lab[r] == P.y[row0 + r]) ? 1u : 0u;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) hits += __shfl_down_sync(0xFFFFFFFFu, hits, o);
+        if (lane == 0 && hits) atomicAdd(P.score, (unsigned long long)hits);
+    }
 }
 
 // ---- the fused pass ----------------------------------------------------------------------------------------------------
@@ -766,52 +837,140 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int sv_bytes) {
         }
     }
     finish_rows_fast<R>(P, SVC, f_svc, zpart, p1, zfin, member[0], unc);
-    unsigned char lab[R];
-    float po[2 * R];
-#pragma unroll
-    for (int r = 0; r < R; ++r) {
-        po[2 * r] = (float)(1.0 - p1[r]);
-        po[2 * r + 1] = (float)p1[r];
-        lab[r] = zfin[r] > 0 ? 1 : 0;
-        if (unc[r]) fixmask |= 1u << r;
-        if (row0 + r >= P.n) continue;
-        if (P.out && !full) { P.out[2 * (row0 + r)] = po[2 * r]; P.out[2 * (row0 + r) + 1] = po[2 * r + 1]; }
-        if (P.out64) { P.out64[2 * (row0 + r)] = 1.0 - p1[r]; P.out64[2 * (row0 + r) + 1] = p1[r]; }
-        if (P.labels) P.labels[row0 + r] = lab[r];
-        if (P.decision) P.decision[row0 + r] = zfin[r];
-        if (P.meta && P.slot_svc >= 0) P.meta[(row0 + r) * P.n_members + P.slot_svc] = member[0][r];
-    }
-    if (P.out && full) {                        // 4 rows x [p0, p1] = two 128-bit stores, 32 contiguous bytes per thread
-        float4* o = reinterpret_cast<float4*>(P.out + 2 * row0);
-        o[0] = make_float4(po[0], po[1], po[2], po[3]);
-        o[1] = make_float4(po[4], po[5], po[6], po[7]);
-    }
-    if (!full) fixmask &= (1u << (unsigned)max(0LL, min((long long)R, P.n - row0))) - 1u;
-    if (nonfinite) fixmask = full ? (1u << R) - 1 : fixmask | ((1u << (unsigned)max(0LL, min((long long)R, P.n - row0))) - 1u);
+    emit_rows<R, double>(P, row0, lane, full, nonfinite, fixmask, p1, zfin, member[0], unc);
+    }   // tile loop
+}
 
-    // ---- rows whose result hinges on a branch go to the work list; hfe_fixup_kernel re-evaluates them in float64 -------
-    if (fixmask) {
+// ---- the streaming pass: stacks without the SVC member (HBM-bound) -------------------------------------------------------
+// Persistent warps, each with its own feature-tile buffer(s) in shared memory.  One lane asks the copy engine for the
+// warp's next 128-row x 17-column tile (cp.async.bulk.tensor.2d + mbarrier complete_tx; SASS UTMALDG) as soon as every
+// lane has read the current one, so no registers are spent on loads in flight and 24 warps fit on an SM; the links and
+// the combiner run in float32.  Measured on B200, 10 M rows: 56 G rows/s = 65 % of the HBM copy bandwidth with 17 bulk
+// copies per tile (the register-window version of hfe_score_kernel<false, ..>: 47 G rows/s).
+#ifndef HFE_STREAM_STAGES
+#define HFE_STREAM_STAGES 1               // measured: 1 stage x 24 warps/SM 51 G rows/s, 2 stages x 12 warps/SM 38 G rows/s
+#endif
+constexpr int STREAM_STAGES = HFE_STREAM_STAGES;
+constexpr int STREAM_TILE_FLOATS = F * WARP_ROWS;
+constexpr size_t STREAM_SMEM_BYTES = (size_t)BLOCK_WARPS * STREAM_STAGES * STREAM_TILE_FLOATS * sizeof(float);
+
+template <int TREE_MODE>
+__global__ void __launch_bounds__(BLOCK_THREADS, HFE_MIN_BLOCKS_STREAM)
+hfe_stream_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ CUtensorMap x_map) {
+    static_assert(TREE_MODE == 0 || TREE_MODE == 1, "general trees keep the x tile of hfe_score_kernel");
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    __shared__ __align__(8) unsigned long long s_full[BLOCK_WARPS][STREAM_STAGES];
+    constexpr int R = ROWS_PER_THREAD;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    float* tiles = reinterpret_cast<float*>(smem_raw) + (size_t)warp * STREAM_STAGES * STREAM_TILE_FLOATS;
+    const int n_tiles = (int)((P.n + WARP_ROWS - 1) / WARP_ROWS);
+    const int stride = gridDim.x * BLOCK_WARPS;
+    const int first = blockIdx.x * BLOCK_WARPS + warp;
+    const bool has_lin = P.slot_lin >= 0;
+
+    // one lane asks for a whole tile with a single 2-D tensor copy (SASS UTMALDG): box = 128 rows x 17 columns of the
+    // [17][ld] matrix, rows at or beyond n are filled with zeros by the copy engine
+    auto issue = [&](int tile, int stage) {
+        const unsigned mbar = (unsigned)__cvta_generic_to_shared(&s_full[warp][stage]);
+        const unsigned dst = (unsigned)__cvta_generic_to_shared(tiles + stage * STREAM_TILE_FLOATS);
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;"
+                     ::"r"(mbar), "r"((unsigned)(STREAM_TILE_FLOATS * sizeof(float))) : "memory");
+        asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                     ::"r"(dst), "l"(&x_map), "r"(tile * WARP_ROWS), "r"(0), "r"(mbar)
+                     : "memory");
+    };
+    if (lane == 0) {
+#pragma unroll
+        for (int st = 0; st < STREAM_STAGES; ++st)
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;"
+                         ::"r"((unsigned)__cvta_generic_to_shared(&s_full[warp][st])));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+#pragma unroll
+        for (int st = 0; st < STREAM_STAGES; ++st)
+            if (first + st * stride < n_tiles) issue(first + st * stride, st);
+    }
+    __syncwarp();
+
+    int k = 0;
+    for (int tile = first; tile < n_tiles; tile += stride, ++k) {
+        const int stage = k % STREAM_STAGES;
+        const unsigned parity = (unsigned)(k / STREAM_STAGES) & 1u;
+        {
+            const unsigned mbar = (unsigned)__cvta_generic_to_shared(&s_full[warp][stage]);
+            asm volatile(
+                "{\n"
+                ".reg .pred p;\n"
+                "TILE_WAIT_%=:\n"
+                "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+                "@p bra TILE_DONE_%=;\n"
+                "bra TILE_WAIT_%=;\n"
+                "TILE_DONE_%=:\n"
+                "}\n" ::"r"(mbar), "r"(parity) : "memory");
+        }
+        const float4* buf = reinterpret_cast<const float4*>(tiles + stage * STREAM_TILE_FLOATS) + lane;
+        const long long row0 = (long long)tile * WARP_ROWS + lane * R;
+        const bool full = (row0 + R <= P.n);
+        const long long row_ld = row0 < P.n ? row0 : 0;
+        const bool needs_fix = P.perm_col >= 0;          // the ragged tail needs nothing: out-of-range rows arrive as zeros
+        double raw[R], zl[R];
+        float finite_probe = 0.f, acc[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) { raw[r] = 0.0; zl[r] = P.lin_intercept; acc[r] = 0.f; }
+#pragma unroll
+        for (int f = 0; f < F; ++f) {
+            float4 v = buf[f * (WARP_ROWS / 4)];
+            if (needs_fix) v = fix_rows4(P, f, row0, row_ld, full, v);
+            float xf[R];
+            xf[0] = v.x; xf[1] = v.y; xf[2] = v.z; xf[3] = v.w;
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                if (has_lin) zl[r] = fma((double)xf[r], P.lin_coef[f], zl[r]);   // NaN/Inf in x makes zl non-finite
+                else finite_probe = fmaf(xf[r], 0.f, finite_probe);
+            }
+            if (TREE_MODE == 1) apply_splits<R>(P, f, xf, acc);
+        }
+        // every lane has read its part of this stage: hand the buffer back to the copy engine for the tile after next
+        __syncwarp();
+        if (lane == 0 && tile + STREAM_STAGES * stride < n_tiles) issue(tile + STREAM_STAGES * stride, stage);
+
+        bool nonfinite = !(finite_probe == 0.f);
+        if (has_lin) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) nonfinite = nonfinite || !(fabs(zl[r]) <= 1.7976931348623157e308);
+        }
+        if (TREE_MODE == 1) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) raw[r] = P.gbt_split_base + (double)acc[r];
+        }
+        // Links and combiner in float32 (MUFU.EX2 / MUFU.RCP + one Newton step): with no SVC member the pass would
+        // otherwise spend most of its instructions on three float64 exponentials per row.  |error| of a link
+        // <= 1.8e-7, of the final probability <= ~4e-7 (bar 1e-6); rows whose |z| is within the (widened) label
+        // guard go to the float64 fix-up like everywhere else.
+        float p1[R], zfin[R], unused_svc[R];
+        bool unc[R];
+        const float b32 = (float)P.final_intercept;
+        const float wg32 = TREE_MODE != 0 ? (float)P.final_coef[TREE_MODE != 0 ? max(P.slot_gbt, 0) : 0] : 0.f;
+        const float wl32 = has_lin ? (float)P.final_coef[max(P.slot_lin, 0)] : 0.f;
+        const float guard32 = (float)P.label_guard;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            if ((fixmask >> r) & 1u) {
-                unsigned slot = atomicAdd(P.status + HFE_STATUS_LIST_LEN, 1u);
-                if (slot < (unsigned)HFE_WORKLIST_CAPACITY) P.status[HFE_STATUS_HEADER_WORDS + slot] = (unsigned)(row0 + r);
-                else atomicOr(P.status, HFE_WORKLIST_OVERFLOW);
+            const float pg = TREE_MODE != 0 ? expit32((float)raw[r]) : 0.f;          // SK/_loss/loss.py:980-998
+            const float pl = has_lin ? expit32((float)zl[r]) : 0.f;                   // SK/linear_model/_base.py:429-451
+            float z = b32;
+            // meta-features are combined in estimators_ order (SK/ensemble/_stacking.py:87-135)
+            if (TREE_MODE != 0 && has_lin && P.slot_lin < P.slot_gbt) { z = fmaf(wl32, pl, z); z = fmaf(wg32, pg, z); }
+            else { if (TREE_MODE != 0) z = fmaf(wg32, pg, z); if (has_lin) z = fmaf(wl32, pl, z); }
+            zfin[r] = z;
+            p1[r] = expit32(z);
+            unc[r] = !(fabsf(z) >= guard32);
+            unused_svc[r] = 0.f;
+            if (P.meta && row0 + r < P.n) {
+                if (P.slot_gbt >= 0) P.meta[(row0 + r) * P.n_members + P.slot_gbt] = (double)pg;
+                if (P.slot_lin >= 0) P.meta[(row0 + r) * P.n_members + P.slot_lin] = (double)pl;
             }
         }
+        emit_rows<R, float>(P, row0, lane, full, nonfinite, 0u, p1, zfin, unused_svc, unc);
     }
-    if (nonfinite) atomicOr(P.status, HFE_ROW_NONFINITE);
-
-    if (P.y && P.score) {                                         // accuracy count; flagged rows are counted by the fix-up
-        unsigned hits = 0;
-#pragma unroll
-        for (int r = 0; r < R; ++r)
-            if (row0 + r < P.n && !((fixmask >> r) & 1u)) hits += (lab[r] == P.y[row0 + r]) ? 1u : 0u;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) hits += __shfl_down_sync(0xFFFFFFFFu, hits, o);
-        if (lane == 0 && hits) atomicAdd(P.score, (unsigned long long)hits);
-    }
-    }   // tile loop
 }
 
 // Second (tiny) launch of every scoring call: one warp per work-list entry re-evaluates that row in float64 and

@@ -768,6 +768,12 @@ inline int build_model(const uint8_t* blob, size_t len, int device, Model** out)
         double w_svc = P.slot_svc >= 0 ? std::fabs(P.final_coef[P.slot_svc]) : 0.0;
         P.label_guard = 2.0 * w_svc * slope * m->svc_guard + 1e-9 +
                         (P.slot_gbt >= 0 ? std::fabs(P.final_coef[P.slot_gbt]) * 0.25 * m->gbt_guard : 0.0);
+        if (P.slot_svc < 0 && m->tree_mode != 2) {
+            // stacks scored by the streaming pass: float32 links (|error| <= 1.8e-7 each) and a float32 combiner logit
+            double w_sum = 0.0;
+            for (int i = 0; i < m->n_members; ++i) w_sum += std::fabs(P.final_coef[i]);
+            P.label_guard += w_sum * 1.8e-7 + (std::fabs(P.final_intercept) + w_sum) * 1.2e-7;
+        }
     }
     if (rc != HFE_OK) {
         for (void* p : m->allocations) cudaFree(p);
