@@ -275,7 +275,9 @@ def run_ours(args):
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as fh:
             t = json.load(fh)
-        traffic = t["dram_bytes_per_row"] * n
+        # per-kernel captures: the fused pass (stacks with the SVC member) and the streaming pass (without)
+        key = "dram_bytes_per_row" if n_sv else "dram_bytes_per_row_stream"
+        traffic = t[key] * n if key in t and int(clf.info.tree_mode) != 2 else None
     except Exception:
         pass
     line = {
@@ -298,7 +300,9 @@ def run_ours(args):
         "gpu_launches": 2 * args.steps * world,      # fused pass + work-list fix-up per step and rank
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                      "frac": achieved / hbm_peak, "traffic": traffic, "peak_source": peak_src,
-                     "kernel": "hfe_score_kernel (fused pass; the work-list fix-up launch that follows takes microseconds)",
+                     "kernel": ("hfe_score_kernel (fused pass" if n_sv or int(clf.info.tree_mode) == 2 else
+                                "hfe_stream_kernel (streaming pass") + "; the work-list fix-up launch that follows takes "
+                               "microseconds)",
                      "bytes_per_row": BYTES_PER_ROW, "avg_launch_ms": avg_launch_ms,
                      "note": ("the RBF-SVC member makes this pass FP32-FMA bound, not HBM bound: see fma_roofline"
                               if n_sv else "no SVC member: this configuration is the HBM-bound part of the ensemble")},

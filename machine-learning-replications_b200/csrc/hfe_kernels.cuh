@@ -42,7 +42,7 @@ constexpr int TREE_CHUNK = 16;            // float32 partial sums over trees are
 #define HFE_PFX_FLUSH 1                   // float32 partial sums go to float64 after every leaf step (1) or every 2nd (2)
 #endif
 #ifndef HFE_MIN_BLOCKS_STREAM
-#define HFE_MIN_BLOCKS_STREAM 5           // streaming pass: register cap; 6 blocks x 4 warps x one 8.5 KB tile stage = 204 KB of shared memory per SM
+#define HFE_MIN_BLOCKS_STREAM 5           // streaming pass: 5 blocks x 4 warps, one 8.5 KB tile buffer per warp (measured: 5 blocks 72 G rows/s, 6 blocks at 80 registers 68 G)
 #endif
 #ifndef HFE_STREAM_TMA
 #define HFE_STREAM_TMA 1                  // SVC-free stacks with stumps / no trees go through hfe_stream_kernel
@@ -845,8 +845,11 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int sv_bytes) {
 // Persistent warps, each with its own feature-tile buffer(s) in shared memory.  One lane asks the copy engine for the
 // warp's next 128-row x 17-column tile (cp.async.bulk.tensor.2d + mbarrier complete_tx; SASS UTMALDG) as soon as every
 // lane has read the current one, so no registers are spent on loads in flight and 24 warps fit on an SM; the links and
-// the combiner run in float32.  Measured on B200, 10 M rows: 56 G rows/s = 65 % of the HBM copy bandwidth with 17 bulk
-// copies per tile (the register-window version of hfe_score_kernel<false, ..>: 47 G rows/s).
+// the combiner run in float32.  Measured on B200, 10 M rows: 72 G rows/s = 84 % of the HBM copy bandwidth (ncu: the kernel alone
+// moves 6.0 TB/s); with 17 one-dimensional bulk copies per tile instead of the tensor copy 56 G rows/s (a fifth of all
+// instructions went into issuing them); the register-window version of hfe_score_kernel<false, ..> 47 G rows/s.  The
+// hot loop is kept small (1.5 k SASS instructions): rare work (permuted column, further splits of a feature) is
+// rolled up and reads the tile with a run-time feature index, which only the shared-memory copy allows.
 #ifndef HFE_STREAM_STAGES
 #define HFE_STREAM_STAGES 1               // measured: 1 stage x 24 warps/SM 51 G rows/s, 2 stages x 12 warps/SM 38 G rows/s
 #endif
@@ -907,29 +910,49 @@ hfe_stream_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__
                 "TILE_DONE_%=:\n"
                 "}\n" ::"r"(mbar), "r"(parity) : "memory");
         }
-        const float4* buf = reinterpret_cast<const float4*>(tiles + stage * STREAM_TILE_FLOATS) + lane;
+        float4* buf = reinterpret_cast<float4*>(tiles + stage * STREAM_TILE_FLOATS) + lane;   // this lane's 4 rows
         const long long row0 = (long long)tile * WARP_ROWS + lane * R;
         const bool full = (row0 + R <= P.n);
-        const long long row_ld = row0 < P.n ? row0 : 0;
-        const bool needs_fix = P.perm_col >= 0;          // the ragged tail needs nothing: out-of-range rows arrive as zeros
+        if (P.perm_col >= 0) {
+            // rare: a permutation-importance pass -- the permuted column is gathered through perm_idx into the tile
+            // (own slots only, so no synchronisation); the ragged tail needs nothing, those rows arrive as zeros
+            const long long row_ld = row0 < P.n ? row0 : 0;
+            buf[P.perm_col * (WARP_ROWS / 4)] =
+                fix_rows4(P, P.perm_col, row0, row_ld, full, make_float4(0.f, 0.f, 0.f, 0.f));
+        }
         double raw[R], zl[R];
         float finite_probe = 0.f, acc[R];
 #pragma unroll
         for (int r = 0; r < R; ++r) { raw[r] = 0.0; zl[r] = P.lin_intercept; acc[r] = 0.f; }
 #pragma unroll
         for (int f = 0; f < F; ++f) {
-            float4 v = buf[f * (WARP_ROWS / 4)];
-            if (needs_fix) v = fix_rows4(P, f, row0, row_ld, full, v);
-            float xf[R];
-            xf[0] = v.x; xf[1] = v.y; xf[2] = v.z; xf[3] = v.w;
+            const float4 v = buf[f * (WARP_ROWS / 4)];
+            const float xf[R] = {v.x, v.y, v.z, v.w};
 #pragma unroll
             for (int r = 0; r < R; ++r) {
                 if (has_lin) zl[r] = fma((double)xf[r], P.lin_coef[f], zl[r]);   // NaN/Inf in x makes zl non-finite
                 else finite_probe = fmaf(xf[r], 0.f, finite_probe);
             }
-            if (TREE_MODE == 1) apply_splits<R>(P, f, xf, acc);
+            if (TREE_MODE == 1) {                       // first merged split of this feature: immediate operands
+                const float thr0 = P.split1_thr[f], dl0 = P.split1_delta[f];
+#pragma unroll
+                for (int r = 0; r < R; ++r)
+                    if (xf[r] <= thr0) acc[r] += dl0;
+            }
+        }
+        if (TREE_MODE == 1) {                           // the remaining splits, any feature: one rolled loop over the tile
+#pragma unroll 1
+            for (int s = 0; s < P.n_extra_splits; ++s) {
+                const float4 v = buf[P.split_feat[s] * (WARP_ROWS / 4)];
+                const float thr = P.split_thr[s], dl = P.split_delta[s];
+                if (v.x <= thr) acc[0] += dl;
+                if (v.y <= thr) acc[1] += dl;
+                if (v.z <= thr) acc[2] += dl;
+                if (v.w <= thr) acc[3] += dl;
+            }
         }
         // every lane has read its part of this stage: hand the buffer back to the copy engine for the tile after next
+        if (P.perm_col >= 0) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // our stores before the engine's
         __syncwarp();
         if (lane == 0 && tile + STREAM_STAGES * stride < n_tiles) issue(tile + STREAM_STAGES * stride, stage);
 

@@ -98,6 +98,9 @@ struct ScoreParams {
     int split_begin[F + 1];                 // the remaining splits of feature f: [split_begin[f], split_begin[f+1])
     float split_thr[MAX_SPLITS];
     float split_delta[MAX_SPLITS];
+    unsigned char split_feat[MAX_SPLITS];   // feature of each remaining split (the streaming pass walks them in one loop)
+    int n_extra_splits;
+    int pad_splits_;
     const uint2* nodes;         // {thr32 bits, feature<<24 | child}: child = GLOBAL index of the left child (right = +1)
     const float* value32;       // lr * value, per node
     const double* value64;
@@ -607,8 +610,10 @@ inline int build_gbt(Model* m, const ParsedBlob& pb, uint32_t idx) {
             }
             P.split_thr[s] = t32;
             P.split_delta[s] = (float)kv.second;
+            P.split_feat[s] = (unsigned char)kv.first.first;
             ++s;
         }
+        P.n_extra_splits = s;
         while (f_cur < F) P.split_begin[++f_cur] = s;
         P.n_splits = (int)merged.size();
         P.gbt_split_base = init_raw + right_sum;

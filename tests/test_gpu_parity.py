@@ -474,6 +474,55 @@ def test_prefix_shared_support_vector_layout(pkg, published, retrained, torch_cu
         clf.close()
 
 
+def test_streaming_pass_for_stacks_without_svc(pkg, published, retrained, torch_cuda):
+    """Stacks without the SVC member go through hfe_stream_kernel (TMA-staged tiles, float32 links): same bars --
+    probabilities <= 1e-6, labels and leaves bit-exact -- at ragged sizes, with a permuted column, NaN rows and the
+    on-device accuracy count."""
+    import torch
+    wm = pkg.synth_models.without_member
+    stacks = []
+    for fx in (published, retrained):
+        no_svc = wm(fx["arrays"], "svc")
+        stacks += [(no_svc, fx["specs"]), (wm(no_svc, "gbt"), fx["specs"]), (wm(no_svc, "linear"), fx["specs"])]
+    for arrays, specs in stacks:
+        clf = pkg.HFStackB200.from_arrays(arrays)
+        assert clf.info.n_support_vectors == 0
+        X = pkg.synth.host_rows(specs, 41, 0, 40_000).astype(np.float64)
+        want = so.predict_proba(arrays, X)
+        got = clf.predict_proba(X)
+        assert np.abs(got - want).max() <= PROBA_TOL
+        assert np.array_equal(clf.predict(X), so.predict(arrays, X))
+        assert np.abs(clf.decision_function(X) - so.decision_function(arrays, X)).max() <= 5e-6
+        assert np.abs(clf.transform(X) - so.transform(arrays, X)).max() <= PROBA_TOL
+        for n in (1, 3, 4, 5, 127, 128, 129, 511, 4099):
+            assert np.abs(clf.predict_proba(X[:n]) - want[:n]).max() <= PROBA_TOL, n
+        bad = X[:300].copy()
+        bad[77, 5] = np.nan
+        with pytest.raises(ValueError):
+            clf.predict_proba(bad)
+        bad[77, 5] = np.inf
+        with pytest.raises(ValueError):
+            clf.predict_proba(bad)
+        # one permutation-importance pass == scoring the materialised shuffle; accuracy counted on device
+        n = 30_001
+        perm = np.random.RandomState(3).permutation(n).astype(np.int32)
+        col = 13
+        Xp = X[:n].copy()
+        Xp[:, col] = X[:n][perm, col]
+        x, xp = clf.to_device_colmajor(X[:n]), clf.to_device_colmajor(Xp)
+        y = so.predict(arrays, Xp).astype(np.uint8)
+        y_dev = torch.from_numpy(y).cuda()
+        out_a = torch.empty((n, 2), dtype=torch.float32, device="cuda")
+        out_b = torch.empty_like(out_a)
+        score = torch.zeros(1, dtype=torch.int64, device="cuda")
+        clf.score_device(x, n=n, perm_col=col, perm_idx=torch.from_numpy(perm).cuda(), out=out_a, y=y_dev, score=score)
+        clf.score_device(xp, n=n, out=out_b)
+        torch.cuda.synchronize()
+        assert torch.equal(out_a, out_b)
+        assert int(score.item()) == n
+        clf.close()
+
+
 def test_integer_cohort_ingest(pkg, published, torch_cuda):
     """int64 (what predict_hf.py:29-36 passes) and uint8 cohort matrices through the device ingest kernels give the
     bytes the float64 route gives; the pinned pipeline accepts them too."""

@@ -60,7 +60,7 @@ def full(rep, tag, title, n_rows, write_traffic):
     rows = list(csv.reader(raw.splitlines()))
     m = {h: (rows[2][i], rows[1][i]) for i, h in enumerate(rows[0])}
     out = [f"# ncu --set full, {title} (round 1)", "",
-           f"`ncu --set full --clock-control none --import-source on -k regex:hfe_score_kernel -s 2 -c 1 python "
+           f"`ncu --set full --clock-control none --import-source on -k regex:hfe_s -s 2 -c 1 python "
            f"tools/ncu_target.py` ({n_rows} synthetic rows; raw metric dump: `r1_{tag}_raw.csv`).", "",
            "| metric | value | unit |", "|---|---:|---|"]
     out += [f"| `{k}` | {m[k][0]} | {m[k][1]} |" for k in KEYS if k in m]
@@ -68,9 +68,12 @@ def full(rep, tag, title, n_rows, write_traffic):
     out += ["", f"DRAM traffic per launch: {tb / 1e6:.1f} MB = **{tb / n_rows:.1f} B/row** against 76 B/row algorithmic "
                 f"(68 read + 8 written).", ""]
     if write_traffic:
-        json.dump({"dram_bytes_per_row": tb / n_rows, "rows": n_rows,
-                   "source": f"profiles/r1_{tag}_raw.csv (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum)"},
-                  open(os.path.join(OUT, "traffic.json"), "w"))
+        path = os.path.join(OUT, "traffic.json")
+        t = json.load(open(path)) if os.path.exists(path) else {}
+        t[write_traffic] = tb / n_rows
+        t[write_traffic + "_source"] = (f"profiles/r1_{tag}_raw.csv ({n_rows} rows, ncu --set full, dram__bytes_read.sum "
+                                        f"+ dram__bytes_write.sum)")
+        json.dump(t, open(path, "w"), indent=1)
     src = subprocess.run(["ncu", "-i", os.path.join(SRC, rep), "--page", "source", "--csv"], capture_output=True,
                          text=True).stdout
     srows = list(csv.reader(src.splitlines()))
@@ -80,7 +83,7 @@ def full(rep, tag, title, n_rows, write_traffic):
     ex = [int(r[ci["Instructions Executed"]] or 0) for r in data]
     hot = [i for i, e in enumerate(ex) if e >= max(ex) * 0.9]
     tot = sum(samples)
-    if len(hot) > 100:
+    if tag == "fused" and len(hot) > 100:
         out += [f"Warp-state samples: RBF leaf loop ({len(hot)} SASS instructions per 4 support vectors) "
                 f"{100 * sum(samples[i] for i in hot) / tot:.1f} %, before it {100 * sum(samples[:hot[0]]) / tot:.1f} %, "
                 f"after it {100 * sum(samples[hot[-1] + 1:]) / tot:.1f} % (with the prefix-shared table layout the "
@@ -91,9 +94,9 @@ def full(rep, tag, title, n_rows, write_traffic):
 if __name__ == "__main__":
     launches()
     full("prof_r1_fused.ncu-rep", "fused", "fused kernel `hfe_score_kernel<SVC, stumps>`, published model (434 support "
-         "vectors)", 4_000_000, True)
-    full("prof_r1_nosvc.ncu-rep", "nosvc", "fused kernel `hfe_score_kernel<no SVC, stumps>` (the HBM-bound configuration)",
-         10_000_000, False)
+         "vectors)", 4_000_000, "dram_bytes_per_row")
+    full("prof_r1_nosvc.ncu-rep", "nosvc", "streaming pass `hfe_stream_kernel<stumps>` (no SVC member: the HBM-bound "
+         "configuration)", 10_000_000, "dram_bytes_per_row_stream")
     for name in ("retrained", "published", "nosvc", "stress", "reference"):
         p = os.path.join(SRC, f"r1_bench_{name}.json")
         if os.path.exists(p):
