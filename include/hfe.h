@@ -138,6 +138,16 @@ int hfe_ingest_rowmajor_i64(const int64_t* x_rowmajor, int64_t n, int32_t n_feat
 int hfe_ingest_rowmajor_u8(const uint8_t* x_rowmajor, int64_t n, int32_t n_features, float* x, int64_t ld,
                            uint32_t* status, void* stream);
 
+/* KNNImputer(missing_values=nan, n_neighbors=1).transform (train_ensemble_public.py:37-40; SK/impute/_knn.py,
+ * SK/metrics/pairwise.py nan_euclidean_distances) on the candidate matrix, before feature selection: x is a row-major
+ * float64 [n, n_features] device matrix imputed in place from the row-major float64 fit matrix fit_x [n_fit,
+ * n_features] (NaN = missing in both).  col_mean[f] = mean of the present values of fit column f, NaN for a column that
+ * is all-missing in fit_x (such columns are left alone; the caller drops them as scikit-learn does).  Among equidistant
+ * donors -- which scikit-learn leaves to np.argpartition, i.e. undefined -- the lowest fit row wins.  The per-device
+ * shared-memory opt-in is done on the first call. */
+int hfe_knn1_impute(const double* fit_x, int64_t n_fit, int32_t n_features, const double* col_mean, double* x,
+                    int64_t n, void* stream);
+
 /* The evaluation train_ensemble_public.py:63-64,67,79 performs next on the probabilities (classification_report of
  * ``y_pred[:,1] > 0.5``, ROC and precision-recall curves): confusion[0..3] = tn, fp, fn, tp at `threshold` (uint64,
  * zeroed by the call); hist (may be NULL) = 2 x HFE_METRIC_BINS uint32, per true class the histogram of P(class 1) in

@@ -7,4 +7,5 @@ from .schema import N_FEATURES, load_cohort_mat, patient_vector  # noqa: F401
 from . import export, shard, synth, synth_models  # noqa: F401
 from . import capi  # noqa: F401,E402
 from .facade import HFStackB200, synth_rows_device  # noqa: F401,E402
-from . import facade, inspection, metrics  # noqa: F401,E402
+from . import facade, impute, inspection, metrics  # noqa: F401,E402
+from .impute import KNNImputerB200  # noqa: F401,E402

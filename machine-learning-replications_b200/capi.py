@@ -21,7 +21,7 @@ METRIC_BINS = 65536
 EXPORTS = [
     "hfe_abi_version", "hfe_last_error_string", "hfe_model_create", "hfe_model_destroy", "hfe_model_get_info",
     "hfe_predict_proba", "hfe_predict", "hfe_score", "hfe_apply", "hfe_predict_proba_f64", "hfe_synth_rows",
-    "hfe_ingest_rowmajor_f64", "hfe_ingest_rowmajor_f32", "hfe_ingest_rowmajor_i64", "hfe_ingest_rowmajor_u8", "hfe_predict_host", "hfe_predict_proba_noalloc", "hfe_binary_metrics",
+    "hfe_ingest_rowmajor_f64", "hfe_ingest_rowmajor_f32", "hfe_ingest_rowmajor_i64", "hfe_ingest_rowmajor_u8", "hfe_knn1_impute", "hfe_predict_host", "hfe_predict_proba_noalloc", "hfe_binary_metrics",
 ]
 
 
@@ -70,6 +70,7 @@ def load_library(path: str = LIB_PATH):
     lib.hfe_ingest_rowmajor_f32.argtypes = [vp, i64, i32, vp, i64, vp, vp]
     lib.hfe_ingest_rowmajor_i64.argtypes = [vp, i64, i32, vp, i64, vp, vp]
     lib.hfe_ingest_rowmajor_u8.argtypes = [vp, i64, i32, vp, i64, vp, vp]
+    lib.hfe_knn1_impute.argtypes = [vp, i64, i32, vp, vp, i64, vp]
     lib.hfe_predict_host.argtypes = [vp, vp, i64, vp, vp, vp, vp]
     lib.hfe_predict_proba_noalloc.argtypes = [vp, vp, i64, i64, vp, vp, vp]
     lib.hfe_binary_metrics.argtypes = [vp, vp, i64, C.c_float, vp, vp, vp]

@@ -356,6 +356,25 @@ int hfe_ingest_rowmajor_u8(const uint8_t* x_rowmajor, int64_t n, int32_t n_featu
     return ingest_common(x_rowmajor, n, n_features, x, ld, status, stream);
 }
 
+int hfe_knn1_impute(const double* fit_x, int64_t n_fit, int32_t n_features, const double* col_mean, double* x,
+                    int64_t n, void* stream) {
+    if (n < 0 || n_fit < 1 || n_features < 1 || n_features > 4096)
+        return fail(HFE_ERR_INVALID_ARGUMENT, "bad imputer sizes");
+    if (n == 0) return HFE_OK;
+    if (!fit_x || !col_mean || !x) return fail(HFE_ERR_INVALID_ARGUMENT, "null imputer buffer");
+    size_t smem = ((size_t)n_features + (size_t)n_fit) * sizeof(double);
+    if (smem > 200 * 1024) return fail(HFE_ERR_TOO_LARGE, "imputer: more fit rows than one block's shared memory holds");
+    static std::once_flag once;
+    std::call_once(once, [] {
+        cudaFuncSetAttribute(hfe_knn1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    });
+    long long blocks = std::min<long long>(n, 148LL * 8);
+    hfe_knn1_kernel<<<(unsigned)blocks, KNN_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(fit_x, n_fit, n_features,
+                                                                                               col_mean, x, n);
+    HFE_CUDA_TRY(cudaGetLastError());
+    return HFE_OK;
+}
+
 int hfe_binary_metrics(const float* proba_n2, const uint8_t* y, int64_t n, float threshold,
                        unsigned long long* confusion, uint32_t* hist, void* stream) {
     if (n < 0 || !confusion) return fail(HFE_ERR_INVALID_ARGUMENT, "bad metrics arguments");

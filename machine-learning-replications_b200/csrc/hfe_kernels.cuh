@@ -474,7 +474,7 @@ constexpr int BLOCK_WARPS = BLOCK_THREADS / 32;
 template <bool SVC, int TREE_MODE, bool PFX>
 __global__ void __launch_bounds__(BLOCK_THREADS, SVC ? (PFX ? HFE_MIN_BLOCKS_PFX : HFE_MIN_BLOCKS) : HFE_MIN_BLOCKS_NOSVC)
 hfe_score_kernel(const __grid_constant__ ScoreParams P, int sv_bytes) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
+    extern __shared__ __align__(128) unsigned char smem_raw[];
     float4* s_sv = reinterpret_cast<float4*>(smem_raw);                       // the support-vector table (sv_bytes)
     float* s_xt = reinterpret_cast<float*>(smem_raw) + (SVC ? (size_t)sv_bytes / 4 : 0);      // [F][BLOCK_ROWS]
 
@@ -1090,6 +1090,84 @@ hfe_ingest_kernel(const T* __restrict__ src, long long n, int nf, float* __restr
     for (int f = 0; f < nf; ++f)
         if ((int)threadIdx.x < rows) dst[(long long)f * ld + r0 + threadIdx.x] = s_tile[threadIdx.x * pitch + f];
     if (bad) atomicOr(status, HFE_ROW_NONFINITE);
+}
+
+// ---- 1-nearest-neighbour imputation (train_ensemble_public.py:37-40: KNNImputer(n_neighbors=1)) ---------------------------
+// One block per receiver row (rows without a missing value return at once).  Phase 1: threads stride over the fit rows
+// and compute the nan-euclidean distance sqrt(F / present * sum_present (x - y)^2) in float64, in the operation order
+// of SK/metrics/pairwise.py (NaN = no shared coordinate), into shared memory.  Phase 2, per missing column: block-wide
+// arg-min over the fit rows that have that column, ties to the lowest row index; the column mean when no distance is
+// defined.  Everything is float64 and row-major, as scikit-learn holds it; this is training-time preprocessing on a few
+// hundred fit rows, so it is written for clarity, not for a roofline.
+constexpr int KNN_THREADS = 128;
+
+__global__ void __launch_bounds__(KNN_THREADS)
+hfe_knn1_kernel(const double* __restrict__ fit, long long n_fit, int nf, const double* __restrict__ col_mean,
+                double* __restrict__ x, long long n) {
+    extern __shared__ double s_knn[];                 // [nf] the receiver row, then [n_fit] distances
+    double* s_row = s_knn;
+    double* s_dist = s_knn + nf;
+    __shared__ double s_best[KNN_THREADS / 32];
+    __shared__ long long s_arg[KNN_THREADS / 32];
+    __shared__ int s_any;
+    const int tid = threadIdx.x;
+    for (long long row = blockIdx.x; row < n; row += gridDim.x) {
+        if (tid == 0) s_any = 0;
+        __syncthreads();
+        bool miss = false;
+        for (int f = tid; f < nf; f += KNN_THREADS) {
+            const double v = x[row * nf + f];
+            s_row[f] = v;
+            miss = miss || (v != v && col_mean[f] == col_mean[f]);      // columns that are all-missing in fit are not imputed
+        }
+        if (miss) s_any = 1;
+        __syncthreads();
+        const int any = s_any;
+        __syncthreads();                               // everyone has read the flag before the next row resets it
+        if (!any) continue;
+        for (long long j = tid; j < n_fit; j += KNN_THREADS) {
+            const double* y = fit + j * nf;
+            double sum = 0.0;
+            int present = 0;
+            for (int f = 0; f < nf; ++f) {
+                const double a = s_row[f], b = y[f];
+                if (a == a && b == b) {
+                    const double d = a - b;
+                    sum = __dadd_rn(sum, __dmul_rn(d, d));
+                    ++present;
+                }
+            }
+            s_dist[j] = present ? __dsqrt_rn(__dmul_rn(__ddiv_rn(sum, (double)present), (double)nf)) : nan("");
+        }
+        __syncthreads();
+        for (int c = 0; c < nf; ++c) {
+            const double v = s_row[c];
+            if (v == v || !(col_mean[c] == col_mean[c])) continue;      // uniform across the block
+            double best = INFINITY;
+            long long arg = -1;
+            for (long long j = tid; j < n_fit; j += KNN_THREADS) {
+                const double d = s_dist[j], yc = fit[j * nf + c];
+                if (yc == yc && d == d && (d < best || (d == best && (arg < 0 || j < arg)))) { best = d; arg = j; }
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const double ob = __shfl_down_sync(0xFFFFFFFFu, best, o);
+                const long long oa = __shfl_down_sync(0xFFFFFFFFu, arg, o);
+                if (oa >= 0 && (arg < 0 || ob < best || (ob == best && oa < arg))) { best = ob; arg = oa; }
+            }
+            if ((tid & 31) == 0) { s_best[tid >> 5] = best; s_arg[tid >> 5] = arg; }
+            __syncthreads();
+            if (tid == 0) {
+                for (int w = 1; w < KNN_THREADS / 32; ++w)
+                    if (s_arg[w] >= 0 && (arg < 0 || s_best[w] < best || (s_best[w] == best && s_arg[w] < arg))) {
+                        best = s_best[w];
+                        arg = s_arg[w];
+                    }
+                x[row * nf + c] = arg >= 0 ? fit[arg * nf + c] : col_mean[c];
+            }
+            __syncthreads();
+        }
+    }
 }
 
 // ---- evaluation counts (what train_ensemble_public.py:63-64,67,79 computes next from the probabilities) ---------------------
