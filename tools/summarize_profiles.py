@@ -23,6 +23,8 @@ KEYS = [
     "smsp__inst_executed.sum", "sm__warps_active.avg.pct_of_peak_sustained_active", "launch__registers_per_thread",
     "launch__grid_size", "launch__block_size", "smsp__warps_eligible.avg.per_cycle_active", "lts__t_sector_hit_rate.pct",
     "l1tex__t_sector_hit_rate.pct", "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum",
+    "l1tex__throughput.avg.pct_of_peak_sustained_elapsed", "lts__throughput.avg.pct_of_peak_sustained_elapsed",
+    "l1tex__t_requests_pipe_lsu_mem_global_op_ld.sum", "l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum",
 ] + [f"smsp__average_warps_issue_stalled_{k}_per_issue_active.ratio" for k in (
     "wait", "math_pipe_throttle", "short_scoreboard", "long_scoreboard", "barrier", "not_selected", "no_instruction",
     "dispatch_stall", "mio_throttle")]
@@ -97,6 +99,9 @@ if __name__ == "__main__":
          "vectors)", 4_000_000, "dram_bytes_per_row")
     full("prof_r1_nosvc.ncu-rep", "nosvc", "streaming pass `hfe_stream_kernel<stumps>` (no SVC member: the HBM-bound "
          "configuration)", 10_000_000, "dram_bytes_per_row_stream")
+    if os.path.exists(os.path.join(SRC, "prof_stress.ncu-rep")):
+        full("prof_stress.ncu-rep", "stress", "fused kernel `hfe_score_kernel<no SVC, general trees>` on the 2000-tree "
+             "stress forest (BASELINE config 4)", 1_000_000, None)
     for name in ("retrained", "published", "nosvc", "stress", "reference"):
         p = os.path.join(SRC, f"r1_bench_{name}.json")
         if os.path.exists(p):
