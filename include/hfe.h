@@ -85,7 +85,9 @@ int hfe_model_get_info(const hfe_model* model, hfe_model_info* out_info);
 /* StackingClassifier.predict_proba (SK/ensemble/_stacking.py:768-794) as called at predict_hf.py:36 and
  * train_ensemble_public.py:62.  out_n2[2*i] = P(class 0) = 1 - p1, out_n2[2*i+1] = p1, float32.
  * One fused kernel: scaler -> RBF-SVC decision -> Platt -> clamp -> 2-class coupling (svm.cpp:2921-2958, 2046-2107),
- * boosted trees (_gradient_boosting.pyx:25-73) -> expit, logistic member (_base.py:366-451), combiner. */
+ * boosted trees (_gradient_boosting.pyx:25-73) -> expit, logistic member (_base.py:366-451), combiner.  Stacks without
+ * the SVC member are bandwidth-bound and take a streaming kernel instead (tiles staged in shared memory by the copy
+ * engine); either way one scoring launch plus the small float64 fix-up launch over the work list. */
 int hfe_predict_proba(const hfe_model* model, const float* x, int64_t n, int64_t ld, float* out_n2,
                       uint32_t* status, void* stream);
 

@@ -121,7 +121,8 @@ int dispatch_score(const Model* m, const ScoreParams& P, cudaStream_t stream) {
     bool svc = P.slot_svc >= 0;
     bool identity = true;                          // the feature order is only changed for stacks with an SVC member
     for (int f = 0; f < F; ++f) identity = identity && m->col_of[f] == f;
-    if (HFE_STREAM_TMA && !svc && m->tree_mode != 2 && identity)
+    // (tensor-copy coordinates are signed 32-bit: beyond 2^31 rows the register-window instance takes over)
+    if (HFE_STREAM_TMA && !svc && m->tree_mode != 2 && identity && P.n < (1LL << 31))
         return m->tree_mode == 0 ? launch_stream<0>(m, P, stream) : launch_stream<1>(m, P, stream);
     if (svc && P.sv_quads > 0) {
         switch (m->tree_mode) {
