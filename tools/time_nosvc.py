@@ -16,4 +16,7 @@ for a, b in ev:
     a.record(); clf.predict_proba_device(x, n=n, out=out, status=st); b.record()
 torch.cuda.synchronize()
 ms = sorted(a.elapsed_time(b) for a, b in ev)[10]
-print(f"{os.environ.get('HFE_LIB','default'):36s} nosvc {ms:.4f} ms {n/ms/1e6:.2f} G rows/s  hbm frac {n*76/ms/1e6/6545.6:.3f}")
+o64 = clf.predict_proba_f64_device(x, n=n)
+err = float((out.double() - o64).abs().max().item())
+print(f"{os.environ.get('HFE_LIB','default'):36s} nosvc {ms:.4f} ms {n/ms/1e6:.2f} G rows/s  hbm frac {n*76/ms/1e6/6545.6:.3f}  "
+      f"fix={int(st[1].item())} maxerr_vs_f64={err:.2e} ({n} rows)")
