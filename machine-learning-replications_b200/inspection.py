@@ -34,10 +34,31 @@ def shuffled_indices(n_samples: int, n_repeats: int, random_seed: int) -> np.nda
     return out
 
 
-def permutation_importance(clf, x, y, n_repeats: int = 5, random_state=None, rank: int = 0, world: int = 1):
+def shuffled_indices_device(n_samples: int, n_repeats: int, random_seed: int, device):
+    """The same composition with the shuffles drawn on the device (``torch.randperm``): not scikit-learn's random
+    stream, but the same procedure -- for cohorts where five host-side Fisher-Yates passes over the row index
+    (~15 ms per million rows each, inherently serial) would dwarf the 86 scoring passes."""
+    import torch
+    gen = torch.Generator(device=device)
+    gen.manual_seed(int(random_seed))
+    eff = torch.arange(n_samples, device=device)
+    out = torch.empty((n_repeats, n_samples), dtype=torch.int32, device=device)
+    for r in range(n_repeats):
+        eff = eff[torch.randperm(n_samples, generator=gen, device=device)]
+        out[r] = eff.to(torch.int32)
+    return out
+
+
+def permutation_importance(clf, x, y, n_repeats: int = 5, random_state=None, rank: int = 0, world: int = 1,
+                           shuffle: str = "sklearn"):
     """``x``: column-major float32 CUDA tensor ``[17, ld]`` (or a numpy ``[n,17]`` array), ``y``: class labels.
+    ``shuffle="sklearn"`` reproduces scikit-learn's permutations exactly (host shuffles); ``shuffle="device"`` draws
+    them on the GPU (same statistics, different random stream; identical on every rank for a given seed).
     Returns an ``ImportanceResult``; with ``world > 1`` torch.distributed must be initialised."""
     import torch
+
+    if shuffle not in ("sklearn", "device"):
+        raise ValueError("shuffle must be 'sklearn' or 'device'")
 
     if isinstance(x, np.ndarray):
         n = x.shape[0]
@@ -49,7 +70,10 @@ def permutation_importance(clf, x, y, n_repeats: int = 5, random_state=None, ran
     y_dev = torch.from_numpy(y_idx).to(dev)
     rs = random_state if isinstance(random_state, np.random.RandomState) else np.random.RandomState(random_state)
     random_seed = rs.randint(np.iinfo(np.int32).max + 1)         # SK/inspection/_permutation_importance.py:278
-    perms = torch.from_numpy(shuffled_indices(n, n_repeats, random_seed)).to(dev)
+    if shuffle == "sklearn":
+        perms = torch.from_numpy(shuffled_indices(n, n_repeats, random_seed)).to(dev)
+    else:
+        perms = shuffled_indices_device(n, n_repeats, random_seed, dev)
     n_feat = clf.n_features_in_
     counts = torch.zeros(1 + n_feat * n_repeats, dtype=torch.int64, device=dev)
     status = clf.new_status()

@@ -317,6 +317,20 @@ def test_permutation_importance_matches_sklearn(pkg, published, clf_for, torch_c
     assert np.array_equal(got.importances.shape, ref.importances.shape)
     assert np.abs(got.importances - ref.importances).max() < 1e-12        # accuracies are integer counts / n
     assert np.abs(got.importances_mean - ref.importances_mean).max() < 1e-12
+    # shuffles drawn on the device: another random stream, the same procedure -- reproducible, statistically the same
+    n = 60_000
+    X = pkg.synth.host_rows(published["specs"], 9, 0, n).astype(np.float64)
+    y = (so.predict_proba(published["arrays"], X)[:, 1] > rng.random(n)).astype(np.float64)
+    clf = clf_for(published)
+    host = pkg.inspection.permutation_importance(clf, X, y, n_repeats=5, random_state=11)
+    dev1 = pkg.inspection.permutation_importance(clf, X, y, n_repeats=5, random_state=11, shuffle="device")
+    dev2 = pkg.inspection.permutation_importance(clf, X, y, n_repeats=5, random_state=11, shuffle="device")
+    assert np.array_equal(dev1.importances, dev2.importances)
+    assert dev1.baseline_score == host.baseline_score
+    spread = 4 * np.sqrt(0.25 / n) + 3 * host.importances_std.max()
+    assert np.abs(dev1.importances_mean - host.importances_mean).max() < spread
+    with pytest.raises(ValueError):
+        pkg.inspection.permutation_importance(clf, X, y, shuffle="numpy")
 
 
 def test_device_metrics_match_sklearn(pkg, published, clf_for, torch_cuda):
