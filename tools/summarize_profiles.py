@@ -109,4 +109,6 @@ if __name__ == "__main__":
     for name in ("scale2", "scale8", "scale8_1b", "scale8_stress", "perm8"):
         p = os.path.join(SRC, f"{name}.json")
         if os.path.exists(p):
-            open(os.path.join(OUT, f"r1_{name}.json"), "w").write(open(p).read().strip().splitlines()[-1] + "\n")
+            lines = [ln for ln in open(p).read().strip().splitlines() if ln.startswith("{")]
+            keep = lines if name == "perm8" else lines[-1:]          # perm8: one line per shuffle mode
+            open(os.path.join(OUT, f"r1_{name}.json"), "w").write("\n".join(keep) + "\n")
