@@ -1,17 +1,23 @@
 // hfe_kernels.cuh -- sm_100a kernels of the scoring path.
 //
-// hfe_score_kernel<SVC, TREE_MODE> is the fused pass: one thread owns ROWS_PER_THREAD (=4) consecutive rows, fetched
+// hfe_score_kernel<SVC, TREE_MODE, PFX> is the fused pass: one thread owns ROWS_PER_THREAD (=4) consecutive rows, fetched
 // from the column-major float32 matrix with one 128-bit load per feature (a warp reads 512 contiguous bytes of each
 // column).  Per row it evaluates, without leaving registers,
 //   a6/a7  StandardScaler + RBF-SVC decision + Platt + clamp + 2-class coupling   (svm.cpp:461-515, 2821-2958, 2046-2107)
 //   a8     boosted trees (merged stump table or general node tables) + expit        (_gradient_boosting.pyx:25-73)
 //   a10    logistic member on the raw features                                       (linear_model/_base.py:366-451)
 //   a11    combiner + hard label (z > 0)                                             (linear_model/_base.py:398-451)
-// and writes [1-p, p] (8 bytes per row).  The RBF sum -- 434 x 17 multiply-adds + 434 exp2 per row, ~98 % of the
-// reference's CPU time -- runs in float32 on the FMA / MUFU pipes out of a shared-memory support-vector table read
-// with warp-broadcast LDS.128; everything after it runs in float64 on B200's full-rate FP64 pipe.
+// and writes [1-p, p] (8 bytes per row).  The RBF sum -- ~98 % of the reference's CPU time -- runs in float32 on the
+// FMA / MUFU pipes out of a shared-memory support-vector table (staged by a TMA bulk copy, read with warp-broadcast
+// LDS.128); with the prefix-shared table layout (PFX, hfe_model.cuh) partial dot products over the leading features are
+// computed once per distinct prefix.  Everything after the sum runs in float64 on B200's full-rate FP64 pipe.
 // Rows whose result could differ from a float64 evaluation by a branch (coupling-solver exit test, label sign) are
-// collected per block and re-evaluated cooperatively in float64 (eval_row_f64) before the block retires.
+// appended to the per-call work list; hfe_fixup_kernel, launched right behind, re-evaluates them in float64.
+//
+// hfe_stream_kernel<TREE_MODE> scores stacks without the SVC member, which are bandwidth-bound: persistent warps,
+// feature tiles staged in shared memory by 2-D TMA tensor copies, float32 links.
+// The remaining kernels are the data-format and evaluation steps either side of the path (ingest, synthetic rows,
+// leaf indices, 1-NN imputation, confusion counts / probability histograms).
 #pragma once
 
 #include <cuda.h>          // CUtensorMap (types only; the encoder is fetched through cudaGetDriverEntryPoint)
