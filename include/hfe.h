@@ -145,8 +145,8 @@ int hfe_ingest_rowmajor_u8(const uint8_t* x_rowmajor, int64_t n, int32_t n_featu
  * float64 [n, n_features] device matrix imputed in place from the row-major float64 fit matrix fit_x [n_fit,
  * n_features] (NaN = missing in both).  col_mean[f] = mean of the present values of fit column f, NaN for a column that
  * is all-missing in fit_x (such columns are left alone; the caller drops them as scikit-learn does).  Among equidistant
- * donors -- which scikit-learn leaves to np.argpartition, i.e. undefined -- the lowest fit row wins.  The per-device
- * shared-memory opt-in is done on the first call. */
+ * donors -- which scikit-learn leaves to np.argpartition, i.e. undefined -- the lowest fit row wins.  At most ~25 000
+ * fit rows (the distances of one receiver row live in one block's shared memory). */
 int hfe_knn1_impute(const double* fit_x, int64_t n_fit, int32_t n_features, const double* col_mean, double* x,
                     int64_t n, void* stream);
 

@@ -365,10 +365,8 @@ int hfe_knn1_impute(const double* fit_x, int64_t n_fit, int32_t n_features, cons
     if (!fit_x || !col_mean || !x) return fail(HFE_ERR_INVALID_ARGUMENT, "null imputer buffer");
     size_t smem = ((size_t)n_features + (size_t)n_fit) * sizeof(double);
     if (smem > 200 * 1024) return fail(HFE_ERR_TOO_LARGE, "imputer: more fit rows than one block's shared memory holds");
-    static std::once_flag once;
-    std::call_once(once, [] {
-        cudaFuncSetAttribute(hfe_knn1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-    });
+    if (smem > 48 * 1024)         // per-device attribute; this is training-time preprocessing, so simply set it per call
+        HFE_CUDA_TRY(cudaFuncSetAttribute(hfe_knn1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     long long blocks = std::min<long long>(n, 148LL * 8);
     hfe_knn1_kernel<<<(unsigned)blocks, KNN_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(fit_x, n_fit, n_features,
                                                                                                col_mean, x, n);
