@@ -26,6 +26,15 @@ int check_matrix(const hfe_model* model, const float* x, int64_t n, int64_t ld) 
     return HFE_OK;
 }
 
+// layout of the mapped pinned block of the few-row host path
+constexpr size_t TINY_OFF_X = 0;
+constexpr size_t TINY_OFF_OUT = TINY_OFF_X + (size_t)TINY_HOST_ROWS * F * sizeof(double);
+constexpr size_t TINY_OFF_DECISION = TINY_OFF_OUT + (size_t)TINY_HOST_ROWS * 2 * sizeof(float);
+constexpr size_t TINY_OFF_META = TINY_OFF_DECISION + (size_t)TINY_HOST_ROWS * sizeof(double);
+constexpr size_t TINY_OFF_LABELS = TINY_OFF_META + (size_t)TINY_HOST_ROWS * MAX_MEMBERS * sizeof(double);
+constexpr size_t TINY_OFF_STATUS = TINY_OFF_LABELS + 64;
+constexpr size_t TINY_BYTES = TINY_OFF_STATUS + 64;
+
 template <bool SVC, int TM, bool PFX>
 int launch_score(const Model* m, const ScoreParams& P, cudaStream_t stream) {
     if (SVC && P.sv_bytes > MAX_SV_TABLE_BYTES)
@@ -238,6 +247,18 @@ int hfe_model_create(const void* blob, size_t blob_bytes, int device, hfe_model*
             cudaGetLastError();                 // no arena: small calls fall back to per-call allocation
         }
     }
+    {   // mapped pinned block for the few-row path (inputs, every optional output, one status word)
+        void* hp = nullptr;
+        void* dp = nullptr;
+        if (cudaHostAlloc(&hp, TINY_BYTES, cudaHostAllocMapped) == cudaSuccess &&
+            cudaHostGetDevicePointer(&dp, hp, 0) == cudaSuccess) {
+            impl->tiny_host = static_cast<unsigned char*>(hp);
+            impl->tiny_dev = static_cast<unsigned char*>(dp);
+        } else {
+            if (hp) cudaFreeHost(hp);
+            cudaGetLastError();                 // no mapped block: few-row calls take the staged path
+        }
+    }
     hfe_model* h = new (std::nothrow) hfe_model{impl};
     if (!h) return fail(HFE_ERR_INVALID_ARGUMENT, "out of host memory");
     *out_model = h;
@@ -249,6 +270,7 @@ void hfe_model_destroy(hfe_model* model) {
     if (model->impl) {
         cudaSetDevice(model->impl->device);
         for (void* p : model->impl->allocations) cudaFree(p);
+        if (model->impl->tiny_host) cudaFreeHost(model->impl->tiny_host);
         delete model->impl;
     }
     delete model;
@@ -444,6 +466,41 @@ int hfe_predict_host(const hfe_model* model, const double* x_rowmajor, int64_t n
     if (!x_rowmajor) return fail(HFE_ERR_INVALID_ARGUMENT, "null input");
     const Model* m = model->impl;
     HFE_CUDA_TRY(cudaSetDevice(m->device));
+    if (n <= TINY_HOST_ROWS && m->tiny_host) {
+        // zero-copy: the rows go into mapped pinned memory, one kernel (a warp per row, float64 path) reads them over
+        // PCIe and writes the results back; what is left is one launch and one synchronisation
+        std::lock_guard<std::mutex> lock(m->small_mutex);
+        unsigned char* hb = m->tiny_host;
+        unsigned char* db = m->tiny_dev;
+        std::memcpy(hb + TINY_OFF_X, x_rowmajor, (size_t)n * F * sizeof(double));
+        *reinterpret_cast<uint32_t*>(hb + TINY_OFF_STATUS) = 0;
+        ScoreParams P = m->base;
+        P.n = n;
+        P.ld = 1;
+        for (int f = 0; f < F; ++f) P.col_off[f] = m->col_of[f];
+        P.out = reinterpret_cast<float*>(db + TINY_OFF_OUT);
+        P.labels = labels ? db + TINY_OFF_LABELS : nullptr;
+        P.decision = decision ? reinterpret_cast<double*>(db + TINY_OFF_DECISION) : nullptr;
+        P.meta = meta ? reinterpret_cast<double*>(db + TINY_OFF_META) : nullptr;
+        hfe_tiny_kernel<<<(unsigned)n, 32, 0, nullptr>>>(P, reinterpret_cast<const double*>(db + TINY_OFF_X),
+                                                             reinterpret_cast<unsigned*>(db + TINY_OFF_STATUS));
+        HFE_CUDA_TRY(cudaGetLastError());
+        HFE_CUDA_TRY(cudaStreamSynchronize(nullptr));
+        if (*reinterpret_cast<volatile uint32_t*>(hb + TINY_OFF_STATUS) & HFE_ROW_NONFINITE)
+            return fail(HFE_ERR_NONFINITE_INPUT, "Input X contains NaN or infinity");
+        const float* o = reinterpret_cast<const float*>(hb + TINY_OFF_OUT);
+        if (proba_n2) {
+            for (int64_t i = 0; i < n; ++i) {
+                double p1 = (double)o[2 * i + 1];
+                proba_n2[2 * i] = 1.0 - p1;
+                proba_n2[2 * i + 1] = p1;
+            }
+        }
+        if (labels) std::memcpy(labels, hb + TINY_OFF_LABELS, (size_t)n);
+        if (decision) std::memcpy(decision, hb + TINY_OFF_DECISION, (size_t)n * sizeof(double));
+        if (meta) std::memcpy(meta, hb + TINY_OFF_META, (size_t)n * m->n_members * sizeof(double));
+        return HFE_OK;
+    }
     int64_t ld = (n + 3) & ~(int64_t)3;
     size_t in_bytes = (size_t)n * F * sizeof(double);
     size_t col_bytes = (size_t)ld * F * sizeof(float);

@@ -359,11 +359,14 @@ __device__ __forceinline__ int walk_tree(const ScoreParams& P, int t, XGet xget)
 // order in which the n_sv kernel values / the trees are summed differs (lane-strided partials + shuffle reduction).
 // All 32 lanes must call it together.  Lane f (< F) holds feature f of the row; other lanes fetch it by shuffle.
 // Returns (on every lane) whether the hard label equals y[row] when y is given.
-__device__ __noinline__ bool eval_row_f64_warp(const ScoreParams& P, long long row) {
+__device__ __noinline__ bool eval_row_f64_warp(const ScoreParams& P, long long row,
+                                               const double* x_rowmajor = nullptr, unsigned* nonfinite_flag = nullptr) {
     const unsigned full_mask = 0xFFFFFFFFu;
     const int lane = threadIdx.x & 31;
     const bool has_svc = P.slot_svc >= 0, has_gbt = P.slot_gbt >= 0, has_lin = P.slot_lin >= 0;
-    float x_mine = lane < F ? load_feature(P, lane, row) : 0.f;
+    // x_rowmajor: a row-major float64 [n, F] source (col_off[] then holds plain column numbers: ld = 1), cast to
+    // float32 like the ingest kernel does
+    float x_mine = lane < F ? (x_rowmajor ? (float)x_rowmajor[row * F + P.col_off[lane]] : load_feature(P, lane, row)) : 0.f;
     double part_svc = 0.0, part_gbt = 0.0;
     if (has_svc) {
         double z[F];
@@ -412,6 +415,7 @@ __device__ __noinline__ bool eval_row_f64_warp(const ScoreParams& P, long long r
         if (!finite) {
             r.p1 = r.z = __longlong_as_double(0x7FF8000000000000LL);
             r.member[0] = r.member[1] = r.member[2] = r.p1;
+            if (nonfinite_flag) atomicOr(nonfinite_flag, HFE_ROW_NONFINITE);
         }
         store_row(P, row, r);
         label = r.z > 0 ? 1 : 0;
@@ -1018,6 +1022,13 @@ hfe_fixup_kernel(const __grid_constant__ ScoreParams P) {
         if (hits && P.score) atomicAdd(P.score, (unsigned long long)hits);
         if (warp == 0) P.status[1] = count;
     }
+}
+
+// A handful of host rows (hfe_predict_host, n <= TINY_HOST_ROWS): one warp per row on the float64 path, reading the
+// row-major float64 input from mapped pinned host memory and writing the outputs back into it.
+__global__ void __launch_bounds__(32)
+hfe_tiny_kernel(const __grid_constant__ ScoreParams P, const double* __restrict__ x_rowmajor, unsigned* status) {
+    eval_row_f64_warp(P, (long long)blockIdx.x, x_rowmajor, status);
 }
 
 // Every row through the float64 path (calibration / test aid; also what hfe_predict_proba_f64 runs).

@@ -43,6 +43,7 @@ constexpr int SV_PREFIX = 9;          // prefix-shared layout: leading (re-order
 constexpr int SV_LEAF_STEPS = F - SV_PREFIX + 1;   // per leaf step: the remaining weights + the folded coefficients
 static_assert(SV_PREFIX % 3 == 0 && SV_LEAF_STEPS % 3 == 0 && SV_STEPS % 3 == 0, "3-deep prefetch ring phase");
 static_assert((F - SV_PREFIX) % 2 == 0, "leaf steps hold two features per float4");
+constexpr int TINY_HOST_ROWS = 32;      // host batches up to this size take the zero-copy single-kernel path
 constexpr int SMALL_HOST_ROWS = 4096;   // host batches up to this size use the model's preallocated staging arena
 constexpr int MAX_EDGES = 16;          // coupling-solver discontinuities (6 exist for eps = 0.0025)
 #ifndef HFE_SV_CHUNK
@@ -137,6 +138,10 @@ struct Model {
     mutable std::mutex small_mutex;
     unsigned char* small_arena = nullptr;
     size_t small_arena_bytes = 0;
+    // a few rows (predict_hf.py scores one patient): pinned host memory mapped into the device address space; one
+    // kernel reads the float64 rows from it and writes every output back into it -- no copies, no second launch
+    unsigned char* tiny_host = nullptr;          // host view
+    unsigned char* tiny_dev = nullptr;           // the same bytes as the device sees them
 };
 
 inline thread_local std::string g_last_error;
