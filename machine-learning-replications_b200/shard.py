@@ -39,6 +39,9 @@ def init_process_group(backend=None):
         if backend is None:
             backend = "nccl" if torch.cuda.is_available() else "gloo"
         if backend == "nccl":
+            # NCCL writes its banner ("NCCL version ...") to stdout when NCCL_DEBUG is set; stdout belongs to the caller
+            # (bench.py prints exactly one JSON line there), so send NCCL's own output to stderr unless told otherwise
+            os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
             torch.cuda.set_device(local_rank)
             dist.init_process_group(backend=backend, rank=rank, world_size=world,
                                     device_id=torch.device("cuda", local_rank))

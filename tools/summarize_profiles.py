@@ -106,7 +106,7 @@ if __name__ == "__main__":
         p = os.path.join(SRC, f"r1_bench_{name}.json")
         if os.path.exists(p):
             open(os.path.join(OUT, f"r1_bench_{name}.json"), "w").write(open(p).read().strip().splitlines()[-1] + "\n")
-    for name in ("scale2", "scale8", "scale8_1b", "scale8_stress", "perm8"):
+    for name in ("scale2", "scale8", "scale8_1b", "scale8_nosvc", "scale8_stress", "perm8"):
         p = os.path.join(SRC, f"{name}.json")
         if os.path.exists(p):
             lines = [ln for ln in open(p).read().strip().splitlines() if ln.startswith("{")]
