@@ -81,6 +81,11 @@ typedef struct hfe_model_info {
 int hfe_model_create(const void* blob, size_t blob_bytes, int device, hfe_model** out_model);
 void hfe_model_destroy(hfe_model* model);
 int hfe_model_get_info(const hfe_model* model, hfe_model_info* out_info);
+/* Host-only twin of hfe_model_create: validates the blob and derives every table exactly as hfe_model_create does, but
+ * touches no device (nothing is uploaded; device_bytes reports what would be).  feature_order (17 entries, may be
+ * NULL) receives the caller's column of each internal feature -- the order the prefix-shared support-vector table was
+ * built for.  For tooling and for tests on machines without a GPU. */
+int hfe_model_plan(const void* blob, size_t blob_bytes, hfe_model_info* out_info, int32_t* feature_order);
 
 /* StackingClassifier.predict_proba (SK/ensemble/_stacking.py:768-794) as called at predict_hf.py:36 and
  * train_ensemble_public.py:62.  out_n2[2*i] = P(class 0) = 1 - p1, out_n2[2*i+1] = p1, float32.

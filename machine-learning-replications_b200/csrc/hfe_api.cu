@@ -276,9 +276,29 @@ void hfe_model_destroy(hfe_model* model) {
     delete model;
 }
 
+static void fill_info(const Model* m, hfe_model_info* info);
+
 int hfe_model_get_info(const hfe_model* model, hfe_model_info* info) {
     if (!model || !model->impl || !info) return fail(HFE_ERR_INVALID_ARGUMENT, "null model or info pointer");
-    const Model* m = model->impl;
+    fill_info(model->impl, info);
+    return HFE_OK;
+}
+
+int hfe_model_plan(const void* blob, size_t blob_bytes, hfe_model_info* out_info, int32_t* feature_order) {
+    if (!blob || !out_info) return fail(HFE_ERR_INVALID_ARGUMENT, "null blob or info pointer");
+    std::vector<uint64_t> copy((blob_bytes + 7) / 8 + 1, 0);
+    std::memcpy(copy.data(), blob, blob_bytes);
+    Model* impl = nullptr;
+    int rc = build_model(reinterpret_cast<const uint8_t*>(copy.data()), blob_bytes, -1, &impl);   // -1: no device work
+    if (rc) return rc;
+    fill_info(impl, out_info);
+    if (feature_order)
+        for (int f = 0; f < F; ++f) feature_order[f] = impl->col_of[f];
+    delete impl;
+    return HFE_OK;
+}
+
+static void fill_info(const Model* m, hfe_model_info* info) {
     std::memset(info, 0, sizeof(*info));
     info->n_features = F;
     info->n_members = m->n_members;
@@ -295,7 +315,6 @@ int hfe_model_get_info(const hfe_model* model, hfe_model_info* info) {
                                                    : 4 * m->base.n_groups * SV_STEPS;
     info->svc_guard = m->svc_guard;
     info->device_bytes = m->device_bytes;
-    return HFE_OK;
 }
 
 int hfe_predict_proba(const hfe_model* model, const float* x, int64_t n, int64_t ld, float* out_n2, uint32_t* status,

@@ -279,6 +279,11 @@ template <typename T>
 inline int upload(Model* m, const std::vector<T>& host, const T** dev) {
     void* p = nullptr;
     size_t bytes = std::max<size_t>(host.size() * sizeof(T), 16);
+    if (m->device < 0) {                        // planning only (hfe_model_plan): sizes are counted, nothing is uploaded
+        m->device_bytes += bytes;
+        *dev = nullptr;
+        return HFE_OK;
+    }
     HFE_CUDA_TRY(cudaMalloc(&p, bytes));
     m->allocations.push_back(p);
     m->device_bytes += bytes;
@@ -727,7 +732,7 @@ inline int build_model(const uint8_t* blob, size_t len, int device, Model** out)
     const Section* cls = pb.find(K_CLASSES, STACK_LEVEL, 2);
     if (!fin || !cls || !all_finite(fin->f64(), pb.n_members + 1))
         return fail(HFE_ERR_BAD_BLOB, "blob: combiner section missing or non-finite");
-    HFE_CUDA_TRY(cudaSetDevice(device));
+    if (device >= 0) HFE_CUDA_TRY(cudaSetDevice(device));
     Model* m = new Model();
     m->device = device;
     m->n_members = (int)pb.n_members;
