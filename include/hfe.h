@@ -164,10 +164,10 @@ int hfe_binary_metrics(const float* proba_n2, const uint8_t* y, int64_t n, float
                        unsigned long long* confusion, uint32_t* hist, void* stream);
 
 /* Host-buffer convenience used by the facade for numpy inputs: copies X (row-major float64, host) to the device,
- * ingests, scores, copies P back (float64 [n,2]; p0 = 1 - p1) and synchronises.  Batches up to 4096 rows use a
- * staging arena that belongs to the handle (one caller at a time), larger ones stream-ordered temporaries; up to 32
- * rows (predict_hf.py:36 scores one patient) skip the copies altogether: the rows are placed in pinned memory mapped
- * into the device address space and one kernel evaluates them on the float64 path and writes the results back.
+ * ingests, scores, copies P back (float64 [n,2]; p0 = 1 - p1) and synchronises.  Large batches use stream-ordered
+ * temporaries.  Up to 4096 rows (predict_hf.py:36 scores one patient) skip the copies altogether: the rows are placed
+ * in pinned memory mapped into the device address space (a block owned by the handle, one caller at a time) and one
+ * kernel -- a warp per row, on the float64 path -- evaluates them and writes the results back.
  * labels / decision / meta may be NULL.  Returns HFE_ERR_NONFINITE_INPUT when X holds NaN/Inf. */
 int hfe_predict_host(const hfe_model* model, const double* x_rowmajor, int64_t n, double* proba_n2, uint8_t* labels,
                      double* decision, double* meta);

@@ -32,7 +32,7 @@ constexpr size_t TINY_OFF_OUT = TINY_OFF_X + (size_t)TINY_HOST_ROWS * F * sizeof
 constexpr size_t TINY_OFF_DECISION = TINY_OFF_OUT + (size_t)TINY_HOST_ROWS * 2 * sizeof(float);
 constexpr size_t TINY_OFF_META = TINY_OFF_DECISION + (size_t)TINY_HOST_ROWS * sizeof(double);
 constexpr size_t TINY_OFF_LABELS = TINY_OFF_META + (size_t)TINY_HOST_ROWS * MAX_MEMBERS * sizeof(double);
-constexpr size_t TINY_OFF_STATUS = TINY_OFF_LABELS + 64;
+constexpr size_t TINY_OFF_STATUS = TINY_OFF_LABELS + (((size_t)TINY_HOST_ROWS + 63) & ~(size_t)63);
 constexpr size_t TINY_BYTES = TINY_OFF_STATUS + 64;
 
 template <bool SVC, int TM, bool PFX>

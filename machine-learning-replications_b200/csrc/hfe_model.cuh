@@ -43,7 +43,10 @@ constexpr int SV_PREFIX = 9;          // prefix-shared layout: leading (re-order
 constexpr int SV_LEAF_STEPS = F - SV_PREFIX + 1;   // per leaf step: the remaining weights + the folded coefficients
 static_assert(SV_PREFIX % 3 == 0 && SV_LEAF_STEPS % 3 == 0 && SV_STEPS % 3 == 0, "3-deep prefetch ring phase");
 static_assert((F - SV_PREFIX) % 2 == 0, "leaf steps hold two features per float4");
-constexpr int TINY_HOST_ROWS = 32;      // host batches up to this size take the zero-copy single-kernel path
+#ifndef HFE_TINY_HOST_ROWS
+#define HFE_TINY_HOST_ROWS 4096           // measured: 1 row 45 us, 1024 rows 58 us (staged path 109 us), 4096 rows 116 us (155 us)
+#endif
+constexpr int TINY_HOST_ROWS = HFE_TINY_HOST_ROWS;      // host batches up to this size take the zero-copy single-kernel path
 constexpr int SMALL_HOST_ROWS = 4096;   // host batches up to this size use the model's preallocated staging arena
 constexpr int MAX_EDGES = 16;          // coupling-solver discontinuities (6 exist for eps = 0.0025)
 #ifndef HFE_SV_CHUNK

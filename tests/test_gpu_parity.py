@@ -33,6 +33,19 @@ def clf_for(pkg, cuda_lib, torch_cuda):
     return make
 
 
+def device_scores(clf, X):
+    """The device protocol (ingest kernel -> fused / streaming kernel -> fix-up) whatever the row count; host calls
+    of up to 4096 rows take the zero-copy float64 path instead."""
+    import torch
+    n = len(X)
+    x = clf.to_device_colmajor(X)
+    out = torch.empty((n, 2), dtype=torch.float32, device="cuda")
+    lab = torch.empty(n, dtype=torch.uint8, device="cuda")
+    clf.score_device(x, n=n, out=out, labels=lab)
+    torch.cuda.synchronize()
+    return out.cpu().numpy().astype(np.float64), lab.cpu().numpy()
+
+
 def test_golden_fixture_parity(case, clf_for):
     clf, g = clf_for(case), case["golden"]
     X = g["X"].astype(np.float64)
@@ -45,6 +58,11 @@ def test_golden_fixture_parity(case, clf_for):
     assert np.abs(clf.transform(X) - g["meta"]).max() <= 2e-6
     assert np.abs(clf.decision_function(X) - so.decision_function(case["arrays"], X)).max() <= 5e-6
     assert np.array_equal(clf.classes_, [0.0, 1.0]) and clf.n_features_in_ == 17
+    # the same rows through the device protocol: float32 RBF sum, guard bands and the work-list fix-up at work on the
+    # rows the fixture places next to every discontinuity
+    dev, dev_labels = device_scores(clf, X)
+    assert np.abs(dev - g["proba"]).max() <= PROBA_TOL
+    assert np.array_equal(clf.classes_[dev_labels], g["label"])
 
 
 def test_predict_hf_default_patient(published, clf_for, pkg):
@@ -55,12 +73,16 @@ def test_predict_hf_default_patient(published, clf_for, pkg):
     assert "{0:.2f}".format(100 * score[0, 1]) == "27.09"
 
 
-@pytest.mark.parametrize("n", [1, 2, 3, 4, 5, 31, 32, 33, 127, 1023, 1024, 1025, 4099])
+@pytest.mark.parametrize("n", [1, 2, 3, 4, 5, 31, 32, 33, 127, 1023, 1024, 1025, 4095, 4096, 4097, 4099])
 def test_ragged_row_counts(published, clf_for, pkg, n):
     X = pkg.synth.host_rows(published["specs"], 11, 777, n).astype(np.float64)
-    got = clf_for(published).predict_proba(X)
-    assert np.abs(got - so.predict_proba(published["arrays"], X)).max() <= PROBA_TOL
-    assert np.array_equal(clf_for(published).predict(X), so.predict(published["arrays"], X))
+    want, want_labels = so.predict_proba(published["arrays"], X), so.predict(published["arrays"], X)
+    got = clf_for(published).predict_proba(X)                    # host protocol
+    assert np.abs(got - want).max() <= PROBA_TOL
+    assert np.array_equal(clf_for(published).predict(X), want_labels)
+    dev, dev_labels = device_scores(clf_for(published), X)       # device protocol: the fused kernel at this size
+    assert np.abs(dev - want).max() <= PROBA_TOL
+    assert np.array_equal(published["arrays"].classes[dev_labels], want_labels)
 
 
 def test_input_layouts_and_dtypes(published, clf_for, pkg):
@@ -167,9 +189,10 @@ def test_solver_edge_rows_take_the_float64_path(published, clf_for, pkg, torch_c
     g = published["golden"]
     X = g["X"][int(g["n_appendix"]) + 1024:].astype(np.float64)        # the edge rows make_golden picked
     clf = clf_for(published)
-    got = clf.predict_proba(X)
     want = g["proba"][int(g["n_appendix"]) + 1024:]
+    got, _ = device_scores(clf, X)                                      # fused kernel + work-list fix-up
     assert np.abs(got - want).max() <= PROBA_TOL
+    assert np.abs(clf.predict_proba(X) - want).max() <= PROBA_TOL       # host protocol
 
 
 def test_pinned_host_pipeline(case, clf_for, pkg, torch_cuda):
@@ -410,8 +433,8 @@ def test_large_support_vector_tables(pkg, published, torch_cuda):
     clf.close()
     too_big = pkg.HFStackB200.from_arrays(with_svs(1600))
     with pytest.raises(pkg.capi.HfeError, match="support-vector table"):
-        too_big.predict_proba(X[:100])
-    # a few rows never touch the shared-memory table (zero-copy float64 path), so they are scored even for this model
+        too_big.predict_proba(X[:5000])
+    # up to 4096 host rows never touch the shared-memory table (zero-copy float64 path): scored even for this model
     big = with_svs(1600)
     few = pkg.HFStackB200.from_arrays(big).predict_proba(X[:8])
     assert np.abs(few - so.predict_proba(big, X[:8])).max() <= 1e-7      # float64 path, float32 output rounding
@@ -514,6 +537,9 @@ def test_streaming_pass_for_stacks_without_svc(pkg, published, retrained, torch_
         assert np.abs(clf.transform(X) - so.transform(arrays, X)).max() <= PROBA_TOL
         for n in (1, 3, 4, 5, 127, 128, 129, 511, 4099):
             assert np.abs(clf.predict_proba(X[:n]) - want[:n]).max() <= PROBA_TOL, n
+            dev, dev_labels = device_scores(clf, X[:n])                      # the streaming kernel at this size
+            assert np.abs(dev - want[:n]).max() <= PROBA_TOL, n
+            assert np.array_equal(arrays.classes[dev_labels], so.predict(arrays, X[:n])), n
         bad = X[:300].copy()
         bad[77, 5] = np.nan
         with pytest.raises(ValueError):
