@@ -20,6 +20,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
+#include <cstdlib>
 #include <cstring>
 #include <functional>
 #include <map>
@@ -421,6 +422,10 @@ inline int build_svc(Model* m, const ParsedBlob& pb, uint32_t idx) {
             for (size_t q = 0; q < sizes.size(); q += 4) steps += sizes[q];
             double cost = pipe_cost(4.0 * (quads * SV_PREFIX + steps * SV_LEAF_STEPS), 5.0 * steps);
             if (best_T == 0 || cost < best_cost) { best_T = T; best_cost = cost; }
+        }
+        if (const char* t_env = std::getenv("HFE_PFX_CHUNK")) {         // development aid: force the chunk size
+            int t = std::atoi(t_env);
+            if (t >= 1 && t <= 255) { best_T = t; best_cost = 0.0; }
         }
         double flat_cost = pipe_cost(4.0 * n_groups * SV_STEPS, 5.0 * n_groups);
         if (best_T > 0 && best_cost < 0.9 * flat_cost) {
