@@ -22,7 +22,7 @@ from .export import ModelArrays, arrays_from_published_pickle, arrays_from_stack
 from .schema import N_FEATURES
 
 
-def _validate_X(X, n_features):
+def _validate_X(X, n_features, check_finite=True):
     """The checks scikit-learn's ``validate_data`` applies on this path, with its messages."""
     arr = np.asarray(X)
     if arr.dtype == object or arr.dtype.kind in "USV":
@@ -43,11 +43,19 @@ def _validate_X(X, n_features):
         raise ValueError(f"X has {arr.shape[1]} features, but HFStackB200 is expecting {n_features} features as "
                          "input.")
     arr = np.ascontiguousarray(arr, dtype=np.float64)
+    if check_finite:
+        _raise_if_not_finite(arr)
+    return arr
+
+
+def _raise_if_not_finite(arr):
+    """scikit-learn's finiteness check with its messages.  The scoring entry points skip this host-side scan (it costs
+    as much as the whole device call on large arrays): the device pass flags non-finite values, and only then is the
+    array scanned here to word the error like scikit-learn does."""
     if not np.isfinite(arr).all():
         if np.isnan(arr).any():
             raise ValueError("Input X contains NaN.")
         raise ValueError("Input X contains infinity or a value too large for dtype('float64').")
-    return arr
 
 
 class HFStackB200:
@@ -102,7 +110,7 @@ class HFStackB200:
 
     # -- numpy (host) protocol -------------------------------------------------------------------------------------
     def _host_call(self, X, want_labels=False, want_decision=False, want_meta=False):
-        arr = _validate_X(X, self.n_features_in_)
+        arr = _validate_X(X, self.n_features_in_, check_finite=False)
         n = arr.shape[0]
         proba = np.empty((n, 2), dtype=np.float64)
         labels = np.empty(n, dtype=np.uint8) if want_labels else None
@@ -115,6 +123,7 @@ class HFStackB200:
         code = self._lib.hfe_predict_host(self._handle, ptr(arr), n, ptr(proba), ptr(labels), ptr(decision),
                                           ptr(meta))
         if code == capi.HFE_ERR_NONFINITE_INPUT:
+            _raise_if_not_finite(arr)
             raise ValueError("Input X contains infinity or a value too large for dtype('float32').")
         capi.check(code)
         return proba, labels, decision, meta
