@@ -12,7 +12,13 @@
  *     hfe_last_error_string() gives the text for the calling thread's last failure.
  *   - pointers named x, out, labels, ... in the *device* entry points are CUDA device pointers on the model's
  *     device; `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream).  Device entry points
- *     only enqueue work: they neither allocate nor synchronise.
+ *     enqueue work on `stream` and return: no device memory is allocated and nothing is waited for.  Host-side set-up
+ *     that is not free: the first scoring call per (device, kernel variant) takes a mutex, opts the kernel in to large
+ *     dynamic shared memory (cudaFuncSetAttribute) and asks the occupancy calculator how many blocks stay resident;
+ *     every call to a stack without the SVC member encodes a tensor map of the caller's matrix on the host
+ *     (cuTensorMapEncodeTiled, ~1 us).  Entry points that take a model handle make the model's device current
+ *     (cudaSetDevice) and leave it current; those without a handle (ingest, synth_rows, knn1_impute, binary_metrics)
+ *     run on whatever device is current, which must be the one that owns the pointers and the stream.
  *   - feature matrices are COLUMN-major float32: feature f of row i lives at x[f*ld + i], ld >= n, ld % 4 == 0 and x
  *     16-byte aligned so that a thread can fetch four consecutive rows of one column with one 128-bit load.
  *   - `status` is a device array of HFE_STATUS_WORDS uint32 (256 KiB) owned by the caller; the call zeroes its header
@@ -101,9 +107,13 @@ int hfe_predict_proba(const hfe_model* model, const float* x, int64_t n, int64_t
 int hfe_predict(const hfe_model* model, const float* x, int64_t n, int64_t ld, uint8_t* labels, float* out_n2,
                 uint32_t* status, void* stream);
 
-/* Everything at once; any output pointer may be NULL.  decision[i] is the combiner's float64 decision value
- * (StackingClassifier.decision_function), meta[i*n_members + m] the float64 P(class 1) of member m
- * (StackingClassifier.transform, SK/ensemble/_stacking.py:814-830, 87-135).
+/* Everything at once; any output pointer may be NULL.  decision[i] is the combiner's decision value
+ * (StackingClassifier.decision_function), meta[i*n_members + m] the P(class 1) of member m
+ * (StackingClassifier.transform, SK/ensemble/_stacking.py:814-830, 87-135), both stored as float64.  Their accuracy is
+ * that of the pass that produced them: with the SVC member the links and the combiner run in float64 and only the RBF
+ * sum is float32 (|error| of decision <~ 1e-6); stacks without the SVC member take the streaming pass, whose links and
+ * combiner run in float32 (~1.8e-7 per link, ~5e-7 on decision) and are widened on store.  Rows inside a guard band
+ * are re-evaluated in float64 either way; hfe_score_f64 gives float64 values for every row.
  * perm_col >= 0 scores the matrix with column perm_col read through perm_idx (int32 row indices, length n): one pass
  * of permutation importance (SK/inspection/_permutation_importance.py:31-76) without materialising the shuffled
  * matrix.  If y (uint8 class indices) and score are given, score[0] += #{labels == y} (uint64) is accumulated. */
@@ -118,6 +128,12 @@ int hfe_apply(const hfe_model* model, const float* x, int64_t n, int64_t ld, uin
 /* Same as evaluating every row through the float64 re-evaluation path (test / calibration aid). */
 int hfe_predict_proba_f64(const hfe_model* model, const float* x, int64_t n, int64_t ld, double* out_n2,
                           uint32_t* status, void* stream);
+
+/* hfe_score's outputs with every row on the float64 path (no float32 RBF sum, no guard bands, no work list): labels,
+ * decision values and member probabilities as an all-float64 evaluation gives them.  The parity harness compares the
+ * fused pass with this on every row (labels must be identical); any output pointer may be NULL. */
+int hfe_score_f64(const hfe_model* model, const float* x, int64_t n, int64_t ld, double* out_n2, uint8_t* labels,
+                  double* decision, double* meta, uint32_t* status, void* stream);
 
 /* Synthetic cohort rows on the device (the reference's .mat cohorts are unpublished): column c of row (row0+i) is
  * base[c] + step[c] * #{k : hash32(seed,row,col_id[c]) >= thr[k]}, k in [thr_off[c], thr_off[c+1]).  All table
@@ -184,9 +200,15 @@ int hfe_predict_host(const hfe_model* model, const double* x_rowmajor, int64_t n
  * It calls no cudaMalloc / cudaFree and no allocating library routine.
  *
  *   - n may be at most HFE_NOALLOC_MAX_ROWS; larger batches are refused with HFE_ERR_TOO_LARGE (split them).
- *   - flags (device pointer to one uint32, may be NULL) receives the error bits the `status[0]` word would hold.
- *   - The first call on each device looks up the block's device address (cudaGetSymbolAddress); make that first call
- *     outside any stream capture.  Later calls only enqueue work on `stream`.
+ *   - flags (device pointer to one uint32, may be NULL) receives the error bits the `status[0]` word would hold:
+ *     HFE_ROW_NONFINITE (those rows' outputs are NaN) and HFE_WORKLIST_OVERFLOW, which means what it means for
+ *     hfe_predict_proba -- more than HFE_WORKLIST_CAPACITY rows needed the float64 re-evaluation, the rows beyond the
+ *     capacity kept their float32-path result, and the batch should be rerun through hfe_predict_proba_f64 (which
+ *     needs a caller-owned status array) or in smaller pieces.  A caller that passes NULL never learns of either.
+ *   - Every call asks the runtime for the block's device address (cudaGetSymbolAddress) with the model's device
+ *     current, so the address is never stale after a device reset in the embedding process; the first such lookup on
+ *     a device loads the library's module there, so make that first call outside any stream capture.  Apart from the
+ *     lookup, calls only enqueue work on `stream`.
  *   - All calls on one GPU share the block.  Each call clears the counters it needs before use, so results never depend
  *     on an earlier call, but two calls whose kernels overlap on the GPU (different streams, or different host
  *     threads) would race on it: keep calls to this entry point on one stream per device, or serialise them.

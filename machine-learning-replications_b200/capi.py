@@ -10,6 +10,7 @@ LIB_PATH = os.environ.get("HFE_LIB") or os.path.join(_HERE, "libhfe.so")   # HFE
 
 HFE_OK = 0
 HFE_ERR_NONFINITE_INPUT = 5
+HFE_ERR_TOO_LARGE = 6
 STATUS_HEADER_WORDS = 4
 WORKLIST_CAPACITY = 65532
 STATUS_WORDS = STATUS_HEADER_WORDS + WORKLIST_CAPACITY      # 65536 uint32 = 256 KiB per call
@@ -20,7 +21,7 @@ METRIC_BINS = 65536
 
 EXPORTS = [
     "hfe_abi_version", "hfe_last_error_string", "hfe_model_create", "hfe_model_destroy", "hfe_model_get_info", "hfe_model_plan",
-    "hfe_predict_proba", "hfe_predict", "hfe_score", "hfe_apply", "hfe_predict_proba_f64", "hfe_synth_rows",
+    "hfe_predict_proba", "hfe_predict", "hfe_score", "hfe_apply", "hfe_predict_proba_f64", "hfe_score_f64", "hfe_synth_rows",
     "hfe_ingest_rowmajor_f64", "hfe_ingest_rowmajor_f32", "hfe_ingest_rowmajor_i64", "hfe_ingest_rowmajor_u8", "hfe_knn1_impute", "hfe_predict_host", "hfe_predict_proba_noalloc", "hfe_binary_metrics",
 ]
 
@@ -66,6 +67,7 @@ def load_library(path: str = LIB_PATH):
     lib.hfe_score.argtypes = [vp, vp, i64, i64, i32, vp, vp, vp, vp, vp, vp, vp, vp, vp]
     lib.hfe_apply.argtypes = [vp, vp, i64, i64, vp, vp]
     lib.hfe_predict_proba_f64.argtypes = [vp, vp, i64, i64, vp, vp, vp]
+    lib.hfe_score_f64.argtypes = [vp, vp, i64, i64, vp, vp, vp, vp, vp, vp]
     lib.hfe_synth_rows.argtypes = [u64, i64, i64, i32, vp, vp, vp, vp, vp, vp, i64, vp]
     lib.hfe_ingest_rowmajor_f64.argtypes = [vp, i64, i32, vp, i64, vp, vp]
     lib.hfe_ingest_rowmajor_f32.argtypes = [vp, i64, i32, vp, i64, vp, vp]

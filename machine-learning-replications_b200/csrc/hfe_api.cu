@@ -6,6 +6,7 @@
 #include <new>
 
 #include "hfe_kernels.cuh"
+#include "hfe_host.cuh"
 
 using namespace hfe;
 
@@ -14,6 +15,17 @@ struct hfe_model {
 };
 
 namespace {
+
+// SM count of the current device (entry points without a model handle run on whatever device is current).
+int sm_count_current() {
+    int dev = 0, sms = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms < 1) {
+        cudaGetLastError();
+        return 148;
+    }
+    return sms;
+}
 
 int check_matrix(const hfe_model* model, const float* x, int64_t n, int64_t ld) {
     if (!model || !model->impl) return fail(HFE_ERR_INVALID_ARGUMENT, "null model handle");
@@ -29,7 +41,7 @@ int check_matrix(const hfe_model* model, const float* x, int64_t n, int64_t ld) 
 // layout of the mapped pinned block of the few-row host path
 constexpr size_t TINY_OFF_X = 0;
 constexpr size_t TINY_OFF_OUT = TINY_OFF_X + (size_t)TINY_HOST_ROWS * F * sizeof(double);
-constexpr size_t TINY_OFF_DECISION = TINY_OFF_OUT + (size_t)TINY_HOST_ROWS * 2 * sizeof(float);
+constexpr size_t TINY_OFF_DECISION = TINY_OFF_OUT + (size_t)TINY_HOST_ROWS * 2 * sizeof(double);
 constexpr size_t TINY_OFF_META = TINY_OFF_DECISION + (size_t)TINY_HOST_ROWS * sizeof(double);
 constexpr size_t TINY_OFF_LABELS = TINY_OFF_META + (size_t)TINY_HOST_ROWS * MAX_MEMBERS * sizeof(double);
 constexpr size_t TINY_OFF_STATUS = TINY_OFF_LABELS + (((size_t)TINY_HOST_ROWS + 63) & ~(size_t)63);
@@ -181,15 +193,17 @@ int score_common(const hfe_model* model, const float* x, int64_t n, int64_t ld, 
     P.y = y;
     P.score = score;
     P.status = status;
+    int sms = 0;
+    HFE_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, m->device));
     if (all_f64) {
-        long long blocks = std::min<long long>(n, 148LL * 64);
+        long long blocks = std::min<long long>(n, (long long)sms * 64);
         hfe_score_f64_kernel<<<(unsigned)blocks, BLOCK_THREADS, 0, s>>>(P);
         HFE_CUDA_TRY(cudaGetLastError());
         return HFE_OK;
     }
     rc = dispatch_score(m, P, s);
     if (rc) return rc;
-    hfe_fixup_kernel<<<148, BLOCK_THREADS, 0, s>>>(P);       // re-evaluates the rows the fused kernel put on the work list
+    hfe_fixup_kernel<<<(unsigned)sms, BLOCK_THREADS, 0, s>>>(P);       // re-evaluates the rows the fused kernel put on the work list
     HFE_CUDA_TRY(cudaGetLastError());
     return HFE_OK;
 }
@@ -208,6 +222,8 @@ int ingest_common(const T* x_rowmajor, int64_t n, int32_t n_features, float* x, 
     if (n == 0) return HFE_OK;
     if (!x_rowmajor || !x) return fail(HFE_ERR_INVALID_ARGUMENT, "null ingest buffer");
     long long blocks = (n + BLOCK_THREADS - 1) / BLOCK_THREADS;
+    static_assert((size_t)BLOCK_THREADS * (64 + 1) * sizeof(float) <= 48 * 1024,
+                  "ingest tile of the widest accepted matrix must fit the default dynamic shared-memory limit");
     size_t smem = (size_t)BLOCK_THREADS * (n_features + 1) * sizeof(float);
     hfe_ingest_kernel<T><<<(unsigned)blocks, BLOCK_THREADS, smem, s>>>(x_rowmajor, n, n_features, x, ld, status);
     HFE_CUDA_TRY(cudaGetLastError());
@@ -260,7 +276,12 @@ int hfe_model_create(const void* blob, size_t blob_bytes, int device, hfe_model*
         }
     }
     hfe_model* h = new (std::nothrow) hfe_model{impl};
-    if (!h) return fail(HFE_ERR_INVALID_ARGUMENT, "out of host memory");
+    if (!h) {
+        for (void* p : impl->allocations) cudaFree(p);
+        if (impl->tiny_host) cudaFreeHost(impl->tiny_host);
+        delete impl;
+        return fail(HFE_ERR_INVALID_ARGUMENT, "out of host memory");
+    }
     *out_model = h;
     return HFE_OK;
 }
@@ -271,6 +292,7 @@ void hfe_model_destroy(hfe_model* model) {
         cudaSetDevice(model->impl->device);
         for (void* p : model->impl->allocations) cudaFree(p);
         if (model->impl->tiny_host) cudaFreeHost(model->impl->tiny_host);
+        delete model->impl->pipe;
         delete model->impl;
     }
     delete model;
@@ -345,6 +367,12 @@ int hfe_predict_proba_f64(const hfe_model* model, const float* x, int64_t n, int
                         status, stream, true);
 }
 
+int hfe_score_f64(const hfe_model* model, const float* x, int64_t n, int64_t ld, double* out_n2, uint8_t* labels,
+                  double* decision, double* meta, uint32_t* status, void* stream) {
+    return score_common(model, x, n, ld, -1, nullptr, nullptr, out_n2, labels, decision, meta, nullptr, nullptr, status,
+                        stream, true);
+}
+
 int hfe_apply(const hfe_model* model, const float* x, int64_t n, int64_t ld, uint16_t* leaves, void* stream) {
     int rc = check_matrix(model, x, n, ld);
     if (rc) return rc;
@@ -371,7 +399,7 @@ int hfe_synth_rows(uint64_t seed, int64_t row0, int64_t n, int32_t n_cols, const
     if (n == 0) return HFE_OK;
     if (!col_id || !base || !step || !thr_off || !thr || !x)
         return fail(HFE_ERR_INVALID_ARGUMENT, "null synth_rows table");
-    long long blocks = std::min<long long>((n + BLOCK_THREADS - 1) / BLOCK_THREADS, 148LL * 16);
+    long long blocks = std::min<long long>((n + BLOCK_THREADS - 1) / BLOCK_THREADS, (long long)sm_count_current() * 16);
     hfe_synth_kernel<<<(unsigned)blocks, BLOCK_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
         seed, row0, n, n_cols, col_id, base, step, thr_off, thr, x, ld);
     HFE_CUDA_TRY(cudaGetLastError());
@@ -408,7 +436,7 @@ int hfe_knn1_impute(const double* fit_x, int64_t n_fit, int32_t n_features, cons
     if (smem > 200 * 1024) return fail(HFE_ERR_TOO_LARGE, "imputer: more fit rows than one block's shared memory holds");
     if (smem > 48 * 1024)         // per-device attribute; this is training-time preprocessing, so simply set it per call
         HFE_CUDA_TRY(cudaFuncSetAttribute(hfe_knn1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    long long blocks = std::min<long long>(n, 148LL * 8);
+    long long blocks = std::min<long long>(n, (long long)sm_count_current() * 8);
     hfe_knn1_kernel<<<(unsigned)blocks, KNN_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(fit_x, n_fit, n_features,
                                                                                                col_mean, x, n);
     HFE_CUDA_TRY(cudaGetLastError());
@@ -423,7 +451,7 @@ int hfe_binary_metrics(const float* proba_n2, const uint8_t* y, int64_t n, float
     if (hist) HFE_CUDA_TRY(cudaMemsetAsync(hist, 0, 2 * METRIC_BINS * sizeof(uint32_t), s));
     if (n == 0) return HFE_OK;
     if (!proba_n2 || !y) return fail(HFE_ERR_INVALID_ARGUMENT, "null metrics input");
-    long long blocks = std::min<long long>((n + 255) / 256, 148LL * 8);
+    long long blocks = std::min<long long>((n + 255) / 256, (long long)sm_count_current() * 8);
     hfe_metrics_kernel<<<(unsigned)blocks, 256, 0, s>>>(proba_n2, y, n, threshold, confusion, hist);
     HFE_CUDA_TRY(cudaGetLastError());
     return HFE_OK;
@@ -437,20 +465,13 @@ int hfe_binary_metrics(const float* proba_n2, const uint8_t* y, int64_t n, float
 static __device__ __align__(256) unsigned int g_noalloc_scratch[HFE_STATUS_WORDS];
 
 namespace {
-constexpr int NOALLOC_MAX_DEVICES = 64;
-std::mutex g_noalloc_mutex;
-unsigned int* g_noalloc_device_ptr[NOALLOC_MAX_DEVICES] = {nullptr};
-
-// Device address of g_noalloc_scratch on `device` (which must be current).  Looked up once per device.
-int noalloc_scratch(int device, unsigned int** out) {
-    if (device < 0 || device >= NOALLOC_MAX_DEVICES) return fail(HFE_ERR_INVALID_ARGUMENT, "device ordinal out of range");
-    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
-    if (!g_noalloc_device_ptr[device]) {
-        void* p = nullptr;
-        HFE_CUDA_TRY(cudaGetSymbolAddress(&p, g_noalloc_scratch));
-        g_noalloc_device_ptr[device] = static_cast<unsigned int*>(p);
-    }
-    *out = g_noalloc_device_ptr[device];
+// Device address of g_noalloc_scratch on the current device.  Asked for on every call: after its first use per device
+// the lookup is a table read inside the runtime (no allocation, no synchronisation), and an address cached here would
+// go stale if the embedding process reset the device or re-created its primary context.
+int noalloc_scratch(unsigned int** out) {
+    void* p = nullptr;
+    HFE_CUDA_TRY(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+    *out = static_cast<unsigned int*>(p);
     return HFE_OK;
 }
 }  // namespace
@@ -464,7 +485,7 @@ int hfe_predict_proba_noalloc(const hfe_model* model, const float* x, int64_t n,
     if (n > 0 && !out_n2) return fail(HFE_ERR_INVALID_ARGUMENT, "null output");
     HFE_CUDA_TRY(cudaSetDevice(model->impl->device));
     unsigned int* scratch = nullptr;
-    int rc = noalloc_scratch(model->impl->device, &scratch);
+    int rc = noalloc_scratch(&scratch);
     if (rc) return rc;
     // score_common clears the header words (error bits, work-list length) on `stream` before the kernels run, so
     // whatever the previous call left in the block cannot leak into this one
@@ -476,6 +497,98 @@ int hfe_predict_proba_noalloc(const hfe_model* model, const float* x, int64_t n,
                                      static_cast<cudaStream_t>(stream)));
     return HFE_OK;
 }
+
+}  // extern "C" (reopened below)
+
+namespace {
+// Large host batches: see hfe_host.cuh.  `all_f64` reruns the batch on the float64 kernel (work-list overflow).
+int predict_host_pipelined(const hfe_model* model, const double* x_rowmajor, int64_t n, double* proba_n2,
+                           uint8_t* labels, double* decision, double* meta, bool all_f64) {
+    const Model* m = model->impl;
+    std::lock_guard<std::mutex> lock(m->pipe_mutex);
+    if (!m->pipe) {
+        int rc = host_pipeline_create(m->device, m->n_members, &m->pipe);
+        if (rc) return rc;
+    }
+    HostPipeline& hp = *m->pipe;
+    const int64_t C = hp.chunk;
+    const int nm = m->n_members;
+    uint32_t flags = 0;
+    struct Drain {                       // whatever happens, no stream still touches the slots when we leave
+        HostPipeline& hp;
+        ~Drain() { for (auto& s : hp.slot) { if (s.busy) cudaStreamSynchronize(s.stream); s.busy = false; } }
+    } drain{hp};
+
+    auto retire = [&](HostSlot& s) -> int {
+        if (!s.busy) return HFE_OK;
+        HFE_CUDA_TRY(cudaEventSynchronize(s.done));
+        s.busy = false;
+        const uint32_t* st = reinterpret_cast<const uint32_t*>(s.h_out + hp.h_off_status);
+        flags |= st[0] | st[HFE_STATUS_HEADER_WORDS];
+        const int64_t begin = s.begin, rows = s.rows;
+        hp.pool->run([&](int t, int T) {
+            const int64_t r0 = rows * t / T, r1 = rows * (t + 1) / T;
+            if (r1 <= r0) return;
+            if (proba_n2)
+                widen_proba(reinterpret_cast<const float*>(s.h_out) + 2 * r0, proba_n2 + 2 * (begin + r0), (size_t)(r1 - r0));
+            if (labels) std::memcpy(labels + begin + r0, s.h_out + hp.h_off_lab + r0, (size_t)(r1 - r0));
+            if (decision)
+                std::memcpy(decision + begin + r0, s.h_out + hp.h_off_dec + r0 * sizeof(double), (size_t)(r1 - r0) * sizeof(double));
+            if (meta)
+                std::memcpy(meta + (begin + r0) * nm, s.h_out + hp.h_off_meta + r0 * nm * sizeof(double),
+                            (size_t)(r1 - r0) * nm * sizeof(double));
+        });
+        return HFE_OK;
+    };
+
+    int k = 0;
+    for (int64_t begin = 0; begin < n; begin += C, ++k) {
+        HostSlot& s = hp.slot[k % HOST_SLOTS];
+        int rc = retire(s);
+        if (rc) return rc;
+        const int64_t rows = std::min(C, n - begin);
+        const double* src = x_rowmajor + begin * F;
+        hp.pool->run([&](int t, int T) {
+            const int64_t e0 = rows * F * t / T, e1 = rows * F * (t + 1) / T;
+            narrow_rows(src + e0, s.h_in + e0, (size_t)(e1 - e0));
+        });
+        float* d_raw = reinterpret_cast<float*>(s.d_buf + hp.off_raw);
+        float* d_col = reinterpret_cast<float*>(s.d_buf + hp.off_col);
+        float* d_out = reinterpret_cast<float*>(s.d_buf + hp.off_out);
+        uint8_t* d_lab = labels ? s.d_buf + hp.off_lab : nullptr;
+        double* d_dec = decision ? reinterpret_cast<double*>(s.d_buf + hp.off_dec) : nullptr;
+        double* d_meta = meta ? reinterpret_cast<double*>(s.d_buf + hp.off_meta) : nullptr;
+        uint32_t* d_status = reinterpret_cast<uint32_t*>(s.d_buf + hp.off_status);     // [ingest header | scoring status]
+        HFE_CUDA_TRY(cudaMemcpyAsync(d_raw, s.h_in, (size_t)rows * F * sizeof(float), cudaMemcpyHostToDevice, s.stream));
+        rc = hfe_ingest_rowmajor_f32(d_raw, rows, F, d_col, C, d_status, s.stream);
+        if (rc) return rc;
+        rc = score_common(model, d_col, rows, C, -1, nullptr, d_out, nullptr, d_lab, d_dec, d_meta, nullptr, nullptr,
+                          d_status + HFE_STATUS_HEADER_WORDS, s.stream, all_f64);
+        if (rc) return rc;
+        HFE_CUDA_TRY(cudaMemcpyAsync(s.h_out, d_out, (size_t)rows * 2 * sizeof(float), cudaMemcpyDeviceToHost, s.stream));
+        if (labels) HFE_CUDA_TRY(cudaMemcpyAsync(s.h_out + hp.h_off_lab, d_lab, (size_t)rows, cudaMemcpyDeviceToHost, s.stream));
+        if (decision)
+            HFE_CUDA_TRY(cudaMemcpyAsync(s.h_out + hp.h_off_dec, d_dec, (size_t)rows * sizeof(double), cudaMemcpyDeviceToHost, s.stream));
+        if (meta)
+            HFE_CUDA_TRY(cudaMemcpyAsync(s.h_out + hp.h_off_meta, d_meta, (size_t)rows * nm * sizeof(double), cudaMemcpyDeviceToHost, s.stream));
+        HFE_CUDA_TRY(cudaMemcpyAsync(s.h_out + hp.h_off_status, d_status, 2 * HFE_STATUS_HEADER_WORDS * sizeof(uint32_t),
+                                     cudaMemcpyDeviceToHost, s.stream));
+        HFE_CUDA_TRY(cudaEventRecord(s.done, s.stream));
+        s.begin = begin;
+        s.rows = rows;
+        s.busy = true;
+    }
+    for (int i = 0; i < HOST_SLOTS; ++i) {               // oldest first
+        int rc = retire(hp.slot[(k + i) % HOST_SLOTS]);
+        if (rc) return rc;
+    }
+    if (flags & HFE_ROW_NONFINITE) return fail(HFE_ERR_NONFINITE_INPUT, "Input X contains NaN or infinity");
+    if ((flags & HFE_WORKLIST_OVERFLOW) && !all_f64) return -1;      // caller reruns on the float64 kernel
+    return HFE_OK;
+}
+}  // namespace
+
+extern "C" {
 
 int hfe_predict_host(const hfe_model* model, const double* x_rowmajor, int64_t n, double* proba_n2, uint8_t* labels,
                      double* decision, double* meta) {
@@ -497,7 +610,8 @@ int hfe_predict_host(const hfe_model* model, const double* x_rowmajor, int64_t n
         P.n = n;
         P.ld = 1;
         for (int f = 0; f < F; ++f) P.col_off[f] = m->col_of[f];
-        P.out = reinterpret_cast<float*>(db + TINY_OFF_OUT);
+        P.out = nullptr;
+        P.out64 = reinterpret_cast<double*>(db + TINY_OFF_OUT);      // the kernel evaluates in float64: hand that back
         P.labels = labels ? db + TINY_OFF_LABELS : nullptr;
         P.decision = decision ? reinterpret_cast<double*>(db + TINY_OFF_DECISION) : nullptr;
         P.meta = meta ? reinterpret_cast<double*>(db + TINY_OFF_META) : nullptr;
@@ -507,18 +621,16 @@ int hfe_predict_host(const hfe_model* model, const double* x_rowmajor, int64_t n
         HFE_CUDA_TRY(cudaStreamSynchronize(nullptr));
         if (*reinterpret_cast<volatile uint32_t*>(hb + TINY_OFF_STATUS) & HFE_ROW_NONFINITE)
             return fail(HFE_ERR_NONFINITE_INPUT, "Input X contains NaN or infinity");
-        const float* o = reinterpret_cast<const float*>(hb + TINY_OFF_OUT);
-        if (proba_n2) {
-            for (int64_t i = 0; i < n; ++i) {
-                double p1 = (double)o[2 * i + 1];
-                proba_n2[2 * i] = 1.0 - p1;
-                proba_n2[2 * i + 1] = p1;
-            }
-        }
+        if (proba_n2) std::memcpy(proba_n2, hb + TINY_OFF_OUT, (size_t)n * 2 * sizeof(double));
         if (labels) std::memcpy(labels, hb + TINY_OFF_LABELS, (size_t)n);
         if (decision) std::memcpy(decision, hb + TINY_OFF_DECISION, (size_t)n * sizeof(double));
         if (meta) std::memcpy(meta, hb + TINY_OFF_META, (size_t)n * m->n_members * sizeof(double));
         return HFE_OK;
+    }
+    if (n >= HOST_PIPE_MIN_ROWS) {
+        int rc = predict_host_pipelined(model, x_rowmajor, n, proba_n2, labels, decision, meta, false);
+        if (rc == -1) rc = predict_host_pipelined(model, x_rowmajor, n, proba_n2, labels, decision, meta, true);
+        return rc;
     }
     int64_t ld = (n + 3) & ~(int64_t)3;
     size_t in_bytes = (size_t)n * F * sizeof(double);

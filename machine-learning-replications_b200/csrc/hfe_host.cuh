@@ -1,0 +1,178 @@
+// hfe_host.cuh -- host side of hfe_predict_host for large batches: the call train_ensemble_public.py:62 makes
+// (clf.predict_proba(X) on a pageable, row-major float64 matrix as load_data_public.py:11-14 yields it).
+//
+// The batch is cut into chunks that travel through a ring of slots.  Per chunk
+//   1. a small pool of host threads narrows the caller's float64 rows to float32 into the slot's pinned buffer
+//      (round-to-nearest, the cast SK/ensemble/_gb.py:1579-1604 applies; 68 instead of 136 bytes per row then cross
+//      PCIe, which is what bounds the whole call),
+//   2. the slot's stream copies the buffer to the device, transposes it (ingest kernel), scores it and copies the
+//      float32 probabilities (and any optional output) back into pinned memory,
+//   3. once that stream is done, the threads widen the probabilities into the caller's float64 [n,2] array
+//      (p0 = 1 - p1 in float64, as SK/linear_model/_base.py:440 computes it) while later chunks are in flight.
+// All buffers belong to the model handle and are allocated on the first large call; one large host call at a time
+// per handle.
+#pragma once
+
+#include <atomic>
+#include <condition_variable>
+#include <functional>
+#include <thread>
+
+#include "hfe_model.cuh"
+
+namespace hfe {
+
+// fork-join pool: run(fn) calls fn(t, T) on T threads (the caller is thread 0) and returns when all are done
+class HostPool {
+public:
+    explicit HostPool(int threads) : n_(std::max(threads, 1)) {
+        for (int t = 1; t < n_; ++t) workers_.emplace_back([this, t] { loop(t); });
+    }
+    ~HostPool() {
+        {
+            std::lock_guard<std::mutex> lock(mu_);
+            stop_ = true;
+            ++epoch_;
+        }
+        cv_.notify_all();
+        for (auto& w : workers_) w.join();
+    }
+    int size() const { return n_; }
+    void run(const std::function<void(int, int)>& fn) {
+        if (n_ == 1) { fn(0, 1); return; }
+        {
+            std::lock_guard<std::mutex> lock(mu_);
+            fn_ = &fn;
+            pending_ = n_ - 1;
+            ++epoch_;
+        }
+        cv_.notify_all();
+        fn(0, n_);
+        std::unique_lock<std::mutex> lock(mu_);
+        done_.wait(lock, [this] { return pending_ == 0; });
+        fn_ = nullptr;
+    }
+
+private:
+    void loop(int t) {
+        unsigned long long seen = 0;
+        for (;;) {
+            const std::function<void(int, int)>* fn;
+            {
+                std::unique_lock<std::mutex> lock(mu_);
+                cv_.wait(lock, [&] { return epoch_ != seen; });
+                seen = epoch_;
+                if (stop_) return;
+                fn = fn_;
+            }
+            (*fn)(t, n_);
+            {
+                std::lock_guard<std::mutex> lock(mu_);
+                if (--pending_ == 0) done_.notify_one();
+            }
+        }
+    }
+    int n_;
+    std::vector<std::thread> workers_;
+    std::mutex mu_;
+    std::condition_variable cv_, done_;
+    const std::function<void(int, int)>* fn_ = nullptr;
+    unsigned long long epoch_ = 0;
+    int pending_ = 0;
+    bool stop_ = false;
+};
+
+constexpr int HOST_SLOTS = 3;                 // chunks in flight: one being narrowed, one on the wire, one being scored
+constexpr int64_t HOST_CHUNK_ROWS = 1 << 18;  // 262 144 rows: 17.8 MB of float32 per slot
+constexpr int64_t HOST_PIPE_MIN_ROWS = 1 << 16;   // smaller batches take the single-shot path
+
+struct HostSlot {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t done = nullptr;
+    float* h_in = nullptr;                    // pinned [chunk, F] float32 row-major
+    unsigned char* h_out = nullptr;           // pinned: probabilities f32 [chunk,2] | labels | decision | meta | status words
+    unsigned char* d_buf = nullptr;           // device: raw rows | column-major | outputs | status
+    int64_t begin = 0, rows = 0;              // the chunk this slot currently carries
+    bool busy = false;
+};
+
+struct HostPipeline {
+    int device = 0;
+    int64_t chunk = HOST_CHUNK_ROWS;
+    size_t off_raw = 0, off_col = 0, off_out = 0, off_lab = 0, off_dec = 0, off_meta = 0, off_status = 0, d_bytes = 0;
+    size_t h_off_lab = 0, h_off_dec = 0, h_off_meta = 0, h_off_status = 0, h_bytes = 0;
+    HostSlot slot[HOST_SLOTS];
+    HostPool* pool = nullptr;
+    ~HostPipeline() {
+        for (auto& s : slot) {
+            if (s.stream) cudaStreamDestroy(s.stream);
+            if (s.done) cudaEventDestroy(s.done);
+            if (s.h_in) cudaFreeHost(s.h_in);
+            if (s.h_out) cudaFreeHost(s.h_out);
+            if (s.d_buf) cudaFree(s.d_buf);
+        }
+        delete pool;
+    }
+};
+
+inline int host_thread_count() {
+    int want = 0;
+    if (const char* e = std::getenv("HFE_HOST_THREADS")) want = std::atoi(e);      // deployment knob, not a layout knob
+    if (want < 1) {
+        cpu_set_t set;
+        int avail = (sched_getaffinity(0, sizeof(set), &set) == 0) ? CPU_COUNT(&set) : (int)std::thread::hardware_concurrency();
+        want = std::min(std::max(avail, 1), 16);
+    }
+    return std::min(want, 64);
+}
+
+inline int host_pipeline_create(int device, int n_members, HostPipeline** out) {
+    auto up = [](size_t b) { return (b + 255) & ~(size_t)255; };
+    HostPipeline* hp = new HostPipeline();
+    hp->device = device;
+    const size_t c = (size_t)hp->chunk;
+    size_t at = 0;
+    hp->off_raw = at;    at += up(c * F * sizeof(float));
+    hp->off_col = at;    at += up(c * F * sizeof(float));
+    hp->off_out = at;    at += up(c * 2 * sizeof(float));
+    hp->off_lab = at;    at += up(c);
+    hp->off_dec = at;    at += up(c * sizeof(double));
+    hp->off_meta = at;   at += up(c * (size_t)n_members * sizeof(double));
+    hp->off_status = at; at += up((HFE_STATUS_WORDS + HFE_STATUS_HEADER_WORDS) * sizeof(uint32_t));
+    hp->d_bytes = at;
+    at = up(c * 2 * sizeof(float));
+    hp->h_off_lab = at;    at += up(c);
+    hp->h_off_dec = at;    at += up(c * sizeof(double));
+    hp->h_off_meta = at;   at += up(c * (size_t)n_members * sizeof(double));
+    hp->h_off_status = at; at += 256;
+    hp->h_bytes = at;
+    for (auto& s : hp->slot) {
+        cudaError_t e = cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaHostAlloc(reinterpret_cast<void**>(&s.h_in), c * F * sizeof(float), cudaHostAllocDefault);
+        if (e == cudaSuccess) e = cudaHostAlloc(reinterpret_cast<void**>(&s.h_out), hp->h_bytes, cudaHostAllocDefault);
+        if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void**>(&s.d_buf), hp->d_bytes);
+        if (e != cudaSuccess) {
+            delete hp;
+            return fail(HFE_ERR_CUDA, std::string("host pipeline buffers: ") + cudaGetErrorString(e));
+        }
+    }
+    hp->pool = new HostPool(host_thread_count());
+    *out = hp;
+    return HFE_OK;
+}
+
+// float64 -> float32, round to nearest (vectorises to vcvtpd2ps)
+inline void narrow_rows(const double* __restrict__ src, float* __restrict__ dst, size_t count) {
+    for (size_t i = 0; i < count; ++i) dst[i] = (float)src[i];
+}
+
+inline void widen_proba(const float* __restrict__ src, double* __restrict__ dst, size_t rows) {
+    for (size_t i = 0; i < rows; ++i) {
+        const double p1 = (double)src[2 * i + 1];
+        dst[2 * i] = 1.0 - p1;
+        dst[2 * i + 1] = p1;
+    }
+}
+
+}  // namespace hfe

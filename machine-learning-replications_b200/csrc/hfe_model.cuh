@@ -124,6 +124,8 @@ struct ScoreParams {
     int pad_;
 };
 
+struct HostPipeline;            // hfe_host.cuh: pinned / device slots and the thread pool of large host calls
+
 struct Model {
     int device = 0;
     int n_members = 0;
@@ -146,6 +148,9 @@ struct Model {
     // kernel reads the float64 rows from it and writes every output back into it -- no copies, no second launch
     unsigned char* tiny_host = nullptr;          // host view
     unsigned char* tiny_dev = nullptr;           // the same bytes as the device sees them
+    // large host batches (train_ensemble_public.py:62 on a big cohort): chunk pipeline, built on first use
+    mutable std::mutex pipe_mutex;
+    mutable HostPipeline* pipe = nullptr;
 };
 
 inline thread_local std::string g_last_error;
@@ -166,8 +171,8 @@ inline int fail(int code, const std::string& msg) {
 
 inline uint32_t crc32_zlib(const uint8_t* p, size_t n) {
     static uint32_t table[8][256];
-    static bool ready = false;
-    if (!ready) {
+    static std::once_flag once;                 // two threads may make their first hfe_model_create call together
+    std::call_once(once, [] {
         for (uint32_t i = 0; i < 256; ++i) {
             uint32_t c = i;
             for (int k = 0; k < 8; ++k) c = (c & 1) ? (0xEDB88320u ^ (c >> 1)) : (c >> 1);
@@ -175,8 +180,7 @@ inline uint32_t crc32_zlib(const uint8_t* p, size_t n) {
         }
         for (uint32_t i = 0; i < 256; ++i)
             for (int t = 1; t < 8; ++t) table[t][i] = (table[t - 1][i] >> 8) ^ table[0][table[t - 1][i] & 0xFF];
-        ready = true;
-    }
+    });
     uint32_t c = 0xFFFFFFFFu;
     while (n >= 8) {
         uint32_t a, b;
@@ -423,10 +427,12 @@ inline int build_svc(Model* m, const ParsedBlob& pb, uint32_t idx) {
             double cost = pipe_cost(4.0 * (quads * SV_PREFIX + steps * SV_LEAF_STEPS), 5.0 * steps);
             if (best_T == 0 || cost < best_cost) { best_T = T; best_cost = cost; }
         }
-        if (const char* t_env = std::getenv("HFE_PFX_CHUNK")) {         // development aid: force the chunk size
+#ifdef HFE_DEV
+        if (const char* t_env = std::getenv("HFE_PFX_CHUNK")) {         // development builds only: force the chunk size
             int t = std::atoi(t_env);
             if (t >= 1 && t <= 255) { best_T = t; best_cost = 0.0; }
         }
+#endif
         double flat_cost = pipe_cost(4.0 * n_groups * SV_STEPS, 5.0 * n_groups);
         if (best_T > 0 && best_cost < 0.9 * flat_cost) {
             struct Chunk { int first, count; };

@@ -208,10 +208,45 @@ class HFStackB200:
             out = torch.empty((n, 2), dtype=torch.float32, device=x.device)
         if status is None:
             status = self.new_status()
+        self._lazy_check()
         capi.check(self._lib.hfe_predict_proba(self._handle, x.data_ptr(), n, x.stride(0), out.data_ptr(),
                                                status.data_ptr(), self._stream()))
         self.last_status = status
+        # one word of the status header, snapshotted behind the call on the same stream: what check() / the next
+        # device call look at (the caller may reuse ``status`` for another call in the meantime)
+        if getattr(self, "_pending", None) is None:
+            self._pending = (torch.zeros(1, dtype=torch.int32, device=x.device), torch.cuda.Event())
+        self._pending[0].copy_(status[:1], non_blocking=True)
+        self._pending[1].record(torch.cuda.current_stream(self.device))
+        self._pending_live = True
         return out
+
+    def _raise_for_flags(self, flags):
+        if flags & capi.ROW_NONFINITE:
+            raise ValueError("Input X contains NaN or infinity.")
+        if flags & capi.WORKLIST_OVERFLOW:
+            raise capi.HfeError(capi.HFE_ERR_TOO_LARGE,
+                                "work list overflow: more than WORKLIST_CAPACITY rows of the last device call needed "
+                                "the float64 re-evaluation and the rows beyond it kept their float32 result; rerun "
+                                "that batch through predict_proba_f64_device")
+
+    def _lazy_check(self):
+        """If the previous ``predict_proba_device`` call has finished, look at its error bits (no waiting)."""
+        if getattr(self, "_pending_live", False) and self._pending[1].query():
+            self._pending_live = False
+            self._raise_for_flags(int(self._pending[0].item()))
+
+    def check(self, status=None):
+        """Wait for the device calls issued so far and raise for their error bits: ``ValueError`` for NaN/Inf input
+        (what the numpy entry points raise), ``HfeError`` for a work-list overflow.  ``status``: a status tensor of a
+        finished call to look at instead of the last ``predict_proba_device`` call's snapshot."""
+        import torch
+        torch.cuda.current_stream(self.device).synchronize()
+        if status is not None:
+            self._raise_for_flags(int(status[0].item()))
+        elif getattr(self, "_pending", None) is not None:
+            self._pending_live = False
+            self._raise_for_flags(int(self._pending[0].item()))
 
     def score_device(self, x, n=None, perm_col=-1, perm_idx=None, out=None, labels=None, decision=None, meta=None,
                      y=None, score=None, status=None):
@@ -304,6 +339,19 @@ class HFStackB200:
         capi.check(self._lib.hfe_predict_proba_f64(self._handle, x.data_ptr(), n, x.stride(0), out.data_ptr(),
                                                    status.data_ptr(), self._stream()))
         return out
+
+    def score_f64_device(self, x, n=None, out=None, labels=None, decision=None, meta=None, status=None):
+        """``hfe_score_f64``: any subset of float64-path outputs (the parity harness's exhaustive label check)."""
+        n = x.shape[1] if n is None else int(n)
+        if status is None:
+            status = self.new_status()
+
+        def p(t):
+            return t.data_ptr() if t is not None else None
+
+        capi.check(self._lib.hfe_score_f64(self._handle, x.data_ptr(), n, x.stride(0), p(out), p(labels), p(decision),
+                                           p(meta), status.data_ptr(), self._stream()))
+        return status
 
     def apply_device(self, x, n=None):
         import torch

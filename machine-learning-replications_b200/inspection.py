@@ -13,6 +13,8 @@ from __future__ import annotations
 
 import numpy as np
 
+from . import capi
+
 
 class ImportanceResult(dict):
     """``importances_mean``, ``importances_std``, ``importances`` like scikit-learn's Bunch, plus ``baseline_score``."""
@@ -78,11 +80,27 @@ def permutation_importance(clf, x, y, n_repeats: int = 5, random_state=None, ran
     counts = torch.zeros(1 + n_feat * n_repeats, dtype=torch.int64, device=dev)
     status = clf.new_status()
     jobs = [(-1, 0)] + [(c, r) for c in range(n_feat) for r in range(n_repeats)]
+    flags = torch.zeros(len(jobs), dtype=torch.int32, device=dev)      # status[0] of every pass (one array is reused)
     for k, (col, rep) in enumerate(jobs):
         if k % world != rank:
             continue
         clf.score_device(x, n=n, perm_col=col, perm_idx=perms[rep] if col >= 0 else None, y=y_dev,
                          score=counts[k:k + 1], status=status)
+        flags[k:k + 1].copy_(status[:1])
+    flags_host = flags.cpu().numpy()
+    if (flags_host & capi.ROW_NONFINITE).any():
+        raise ValueError("Input X contains NaN or infinity.")          # what scikit-learn's scorer raises
+    for k in np.nonzero(flags_host & capi.WORKLIST_OVERFLOW)[0]:
+        # more rows than the work list holds needed float64 in this pass: the count is short by the rows beyond the
+        # capacity, so recount the pass from the all-float64 labels of the materialised shuffle
+        col, rep = jobs[k]
+        xp = x
+        if col >= 0:
+            xp = x.clone()
+            xp[col, :n] = x[col, perms[rep].long()]
+        lab = torch.empty(n, dtype=torch.uint8, device=dev)
+        clf.score_f64_device(xp, n=n, labels=lab)
+        counts[k] = (lab == y_dev).sum()
     if world > 1:
         torch.distributed.all_reduce(counts)
     acc = counts.cpu().numpy().astype(np.float64) / n

@@ -23,9 +23,10 @@ def device_counts(proba, y, threshold=0.5, want_hist=True):
     dev = proba.device
     conf = torch.zeros(4, dtype=torch.int64, device=dev)
     hist = torch.zeros((2, capi.METRIC_BINS), dtype=torch.int32, device=dev) if want_hist else None
-    capi.check(lib.hfe_binary_metrics(proba.data_ptr(), y.data_ptr(), n, float(threshold), conf.data_ptr(),
-                                      hist.data_ptr() if want_hist else None,
-                                      torch.cuda.current_stream(dev).cuda_stream))
+    with torch.cuda.device(dev):            # the entry point runs on the current device: make it the tensors' device
+        capi.check(lib.hfe_binary_metrics(proba.data_ptr(), y.data_ptr(), n, float(threshold), conf.data_ptr(),
+                                          hist.data_ptr() if want_hist else None,
+                                          torch.cuda.current_stream(dev).cuda_stream))
     return conf.cpu().numpy().reshape(2, 2), (hist.cpu().numpy().astype(np.int64) if want_hist else None)
 
 

@@ -182,6 +182,27 @@ def test_large_batch_properties(case, clf_for, pkg, torch_cuda):
     torch.cuda.synchronize()
     assert np.array_equal(lab[torch.from_numpy(idx).cuda()].cpu().numpy(),
                           (so.decision_function(case["arrays"], Xs) > 0).astype(np.uint8))
+    # exhaustive: hard labels of the fast pass == labels of the all-float64 pass on EVERY row (SK/linear_model/
+    # _base.py:398-425, z > 0), and the margin the label guard really has: the smallest |z| among rows the fast pass
+    # did not hand to the float64 fix-up against the largest |z_fast - z_f64| seen on such rows
+    dec = torch.empty(n, dtype=torch.float64, device="cuda")
+    st2 = clf.new_status()
+    clf.score_device(x, n=n, labels=lab, decision=dec, status=st2)
+    lab64 = torch.empty(n, dtype=torch.uint8, device="cuda")
+    dec64 = torch.empty(n, dtype=torch.float64, device="cuda")
+    clf.score_f64_device(x, n=n, labels=lab64, decision=dec64)
+    torch.cuda.synchronize()
+    assert torch.equal(lab, lab64)
+    listed = st2[4:4 + int(st2[2].item())].long()
+    assert int(st2[2].item()) <= pkg.capi.WORKLIST_CAPACITY
+    unflagged = torch.ones(n, dtype=torch.bool, device="cuda")
+    unflagged[listed] = False
+    assert float((dec[listed] - dec64[listed]).abs().max().item()) == 0.0        # fix-up rows carry the float64 value
+    worst_err = float((dec - dec64).abs()[unflagged].max().item())
+    closest = float(dec64.abs()[unflagged].min().item())
+    print(f"[{case['name']}] label guard margin: min |z| unflagged {closest:.3e} / max |z32 - z64| {worst_err:.3e} "
+          f"= {closest / worst_err:.1f}x; {int(st2[2].item())} rows re-evaluated")
+    assert closest > 2.0 * worst_err
 
 
 def test_solver_edge_rows_take_the_float64_path(published, clf_for, pkg, torch_cuda):
@@ -211,6 +232,39 @@ def test_pinned_host_pipeline(case, clf_for, pkg, torch_cuda):
     bad[123456, 5] = np.nan
     with pytest.raises(ValueError):
         clf.predict_proba_pinned(torch.from_numpy(bad).pin_memory())
+
+
+def test_large_host_batches_take_the_chunk_pipeline(case, clf_for, pkg, torch_cuda):
+    """train_ensemble_public.py:62 on a big cohort: a pageable float64 numpy matrix through hfe_predict_host's chunk
+    pipeline (host threads narrow to float32 into pinned slots, three chunks in flight) gives the bytes the device
+    protocol gives, for every output kind, at sizes around the chunk boundaries."""
+    torch = torch_cuda
+    clf = clf_for(case)
+    n = (1 << 18) * 2 + 4099                                       # two full chunks and a ragged third
+    X = pkg.synth.host_rows(case["specs"], 17, 0, n).astype(np.float64)
+    x = clf.to_device_colmajor(X)
+    out = torch.empty((n, 2), dtype=torch.float32, device="cuda")
+    lab = torch.empty(n, dtype=torch.uint8, device="cuda")
+    dec = torch.empty(n, dtype=torch.float64, device="cuda")
+    meta = torch.empty((n, 3), dtype=torch.float64, device="cuda")
+    clf.score_device(x, n=n, out=out, labels=lab, decision=dec, meta=meta)
+    torch.cuda.synchronize()
+    proba = clf.predict_proba(X)
+    assert proba.dtype == np.float64 and proba.shape == (n, 2)
+    assert np.array_equal(proba[:, 1], out[:, 1].cpu().numpy().astype(np.float64))
+    assert np.array_equal(proba[:, 0], 1.0 - proba[:, 1])
+    assert np.array_equal(clf.predict(X), clf.classes_[lab.cpu().numpy()])
+    assert np.array_equal(clf.decision_function(X), dec.cpu().numpy())
+    assert np.array_equal(clf.transform(X), meta.cpu().numpy())
+    for m in ((1 << 16), (1 << 16) + 1, (1 << 18), (1 << 18) + 1):
+        assert np.array_equal(clf.predict_proba(X[:m]), proba[:m]), m
+    idx = np.arange(0, n, 97)
+    assert np.abs(proba[idx] - so.predict_proba(case["arrays"], X[idx])).max() <= PROBA_TOL
+    bad = X[:200_000].copy()
+    bad[150_000, 7] = np.inf
+    with pytest.raises(ValueError):
+        clf.predict_proba(bad)
+    assert np.array_equal(clf.predict_proba(X[:70_000]), proba[:70_000])      # the pipeline is reusable after an error
 
 
 def test_permuted_column_pass_and_score_count(published, clf_for, pkg, torch_cuda):
