@@ -231,10 +231,16 @@ class HFStackB200:
                                 "that batch through predict_proba_f64_device")
 
     def _lazy_check(self):
-        """If the previous ``predict_proba_device`` call has finished, look at its error bits (no waiting)."""
+        """If the previous ``predict_proba_device`` call has finished, look at its error bits (no waiting).  A work-list
+        overflow of that call is reported as a ``RuntimeWarning`` here -- the caller never asked about it, and its
+        non-finite rows are visible as NaN outputs anyway; ``check()`` raises."""
         if getattr(self, "_pending_live", False) and self._pending[1].query():
             self._pending_live = False
-            self._raise_for_flags(int(self._pending[0].item()))
+            if int(self._pending[0].item()) & capi.WORKLIST_OVERFLOW:
+                import warnings
+                warnings.warn("the previous predict_proba_device call overflowed its work list: rows beyond "
+                              "WORKLIST_CAPACITY kept their float32-path result; rerun that batch through "
+                              "predict_proba_f64_device (clf.check() raises for this)", RuntimeWarning, stacklevel=3)
 
     def check(self, status=None):
         """Wait for the device calls issued so far and raise for their error bits: ``ValueError`` for NaN/Inf input

@@ -454,6 +454,13 @@ def test_work_list_overflow_falls_back_to_float64(pkg, published, clf_for, torch
     clf.predict_proba_device(xb, n=big.shape[0], status=st)
     torch.cuda.synchronize()
     assert int(st[0].item()) & pkg.capi.WORKLIST_OVERFLOW
+    with pytest.raises(pkg.capi.HfeError, match="work list overflow"):        # the facade surfaces it on request ...
+        clf.check()
+    clf.predict_proba_device(xb, n=big.shape[0], status=st)
+    torch.cuda.synchronize()
+    with pytest.warns(RuntimeWarning, match="overflowed its work list"):      # ... and on the next device call
+        clf.predict_proba_device(x, n=edge.shape[0], status=st)
+    torch.cuda.synchronize()
     want = np.tile(so.predict_proba(published["arrays"], flagged), (reps, 1))
     assert np.abs(clf.predict_proba(big) - want).max() <= PROBA_TOL           # host path: automatic float64 rerun
     got = clf.predict_proba_pinned(torch.from_numpy(big.astype(np.float32)).pin_memory()).numpy()
