@@ -20,7 +20,7 @@ NOALLOC_MAX_ROWS = 1 << 26
 METRIC_BINS = 65536
 
 EXPORTS = [
-    "hfe_abi_version", "hfe_last_error_string", "hfe_model_create", "hfe_model_destroy", "hfe_model_get_info", "hfe_model_plan",
+    "hfe_abi_version", "hfe_last_error_string", "hfe_model_create", "hfe_model_destroy", "hfe_model_get_info", "hfe_model_plan", "hfe_model_set_rbf_engine",
     "hfe_predict_proba", "hfe_predict", "hfe_score", "hfe_apply", "hfe_predict_proba_f64", "hfe_score_f64", "hfe_synth_rows",
     "hfe_ingest_rowmajor_f64", "hfe_ingest_rowmajor_f32", "hfe_ingest_rowmajor_i64", "hfe_ingest_rowmajor_u8", "hfe_knn1_impute", "hfe_predict_host", "hfe_predict_proba_noalloc", "hfe_binary_metrics",
 ]
@@ -38,6 +38,7 @@ class ModelInfo(C.Structure):
         ("n_support_vectors", C.c_int32), ("n_trees", C.c_int32), ("n_tree_nodes", C.c_int32),
         ("max_tree_depth", C.c_int32), ("tree_mode", C.c_int32), ("n_merged_splits", C.c_int32),
         ("device", C.c_int32), ("rbf_fma_per_row", C.c_int32), ("svc_guard", C.c_double), ("device_bytes", C.c_uint64),
+        ("rbf_engine", C.c_int32), ("reserved_", C.c_int32),
     ]
 
 
@@ -61,6 +62,7 @@ def load_library(path: str = LIB_PATH):
     lib.hfe_model_destroy.argtypes = [vp]
     lib.hfe_model_destroy.restype = None
     lib.hfe_model_get_info.argtypes = [vp, C.POINTER(ModelInfo)]
+    lib.hfe_model_set_rbf_engine.argtypes = [vp, C.c_int]
     lib.hfe_model_plan.argtypes = [vp, C.c_size_t, C.POINTER(ModelInfo), C.POINTER(C.c_int32)]
     lib.hfe_predict_proba.argtypes = [vp, vp, i64, i64, vp, vp, vp]
     lib.hfe_predict.argtypes = [vp, vp, i64, i64, vp, vp, vp, vp]

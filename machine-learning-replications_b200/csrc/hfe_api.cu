@@ -6,6 +6,7 @@
 #include <new>
 
 #include "hfe_kernels.cuh"
+#include "hfe_mma.cuh"
 #include "hfe_host.cuh"
 
 using namespace hfe;
@@ -138,8 +139,37 @@ int launch_stream(const Model* m, const ScoreParams& P, cudaStream_t stream) {
     return HFE_OK;
 }
 
+// The RBF sum on the tensor cores (hfe_mma.cuh): one persistent CTA per SM.
+template <int TM>
+int launch_mma(const Model* m, const ScoreParams& P, cudaStream_t stream) {
+    const MmaParams& Q = m->mma;
+    const size_t smem = (((size_t)Q.w_bytes + 1023) & ~(size_t)1023) + (size_t)MMA_A_STAGES * MMA_A_STAGE_BYTES +
+                        4 * (size_t)MMA_SIDE_BYTES + 32 * sizeof(unsigned long long) + 64;
+    auto kernel = hfe_mma_kernel<TM>;
+    static std::mutex mu;
+    static std::map<int, int> ready;
+    int sms = 0;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        if (!ready.count(m->device)) {
+            HFE_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+            ready[m->device] = 1;
+        }
+    }
+    HFE_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, m->device));
+    const long long tiles = (P.n + MMA_TILE_ROWS - 1) / MMA_TILE_ROWS;
+    const long long blocks = std::min<long long>(tiles, sms);
+    kernel<<<(unsigned)blocks, MMA_THREADS, smem, stream>>>(P, Q);
+    HFE_CUDA_TRY(cudaGetLastError());
+    return HFE_OK;
+}
+
 int dispatch_score(const Model* m, const ScoreParams& P, cudaStream_t stream) {
     bool svc = P.slot_svc >= 0;
+    if (svc && m->mma.nb > 0 && m->tree_mode != 2 && m->rbf_engine != 1)
+        return m->tree_mode == 0 ? launch_mma<0>(m, P, stream) : launch_mma<1>(m, P, stream);
+    if (svc && m->rbf_engine == 2)
+        return fail(HFE_ERR_UNSUPPORTED, "the tensor-core RBF path needs at most 512 support vectors and no general tree tables");
     bool identity = true;                          // the feature order is only changed for stacks with an SVC member
     for (int f = 0; f < F; ++f) identity = identity && m->col_of[f] == f;
     // (tensor-copy coordinates are signed 32-bit: beyond 2^31 rows the register-window instance takes over)
@@ -306,6 +336,13 @@ int hfe_model_get_info(const hfe_model* model, hfe_model_info* info) {
     return HFE_OK;
 }
 
+int hfe_model_set_rbf_engine(hfe_model* model, int engine) {
+    if (!model || !model->impl) return fail(HFE_ERR_INVALID_ARGUMENT, "null model handle");
+    if (engine < 0 || engine > 2) return fail(HFE_ERR_INVALID_ARGUMENT, "engine must be 0 (automatic), 1 (SIMT) or 2 (tensor cores)");
+    model->impl->rbf_engine = engine;
+    return HFE_OK;
+}
+
 int hfe_model_plan(const void* blob, size_t blob_bytes, hfe_model_info* out_info, int32_t* feature_order) {
     if (!blob || !out_info) return fail(HFE_ERR_INVALID_ARGUMENT, "null blob or info pointer");
     std::vector<uint64_t> copy((blob_bytes + 7) / 8 + 1, 0);
@@ -337,6 +374,7 @@ static void fill_info(const Model* m, hfe_model_info* info) {
                                                    : 4 * m->base.n_groups * SV_STEPS;
     info->svc_guard = m->svc_guard;
     info->device_bytes = m->device_bytes;
+    info->rbf_engine = m->n_sv == 0 ? 0 : (m->mma.nb > 0 && m->tree_mode != 2 && m->rbf_engine != 1) ? 2 : 1;
 }
 
 int hfe_predict_proba(const hfe_model* model, const float* x, int64_t n, int64_t ld, float* out_n2, uint32_t* status,

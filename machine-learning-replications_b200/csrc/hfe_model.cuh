@@ -124,6 +124,21 @@ struct ScoreParams {
     int pad_;
 };
 
+// Tensor-core path of the RBF sum (hfe_mma.cuh): the B operand image and what the producers need to build the A operand.
+constexpr int MMA_BLOCK_SV = 64;      // support vectors per TMEM region (N of one MMA instruction)
+constexpr int MMA_MAX_SV = 512;       // 8 blocks x [hi | rest] accumulators = the 512 TMEM columns, 4 regions in flight
+constexpr int MMA_B_CHUNKS = 10;      // 16-byte K chunks per support vector: WH0 WH1 WH2 0 | WM0 WM1 WM2 WL0 WL1 WL2
+
+struct MmaParams {
+    const unsigned char* w_img;     // [n_pad/8][MMA_B_CHUNKS][8][16 B] bfloat16 B operand, then float coef[n_pad]
+    int w_bytes;                    // image + coefficient table
+    int nb;                         // blocks of MMA_BLOCK_SV support vectors; n_pad = 64 * nb; 0 = path not available
+    float center[F];                // m_d: the scaler mean rounded to an integer
+    double dmean[F];                // m_d - mean_d
+    double inv_var[F];              // 1 / scale_d^2
+    double neg_c;                   // -gamma * log2(e)
+};
+
 struct HostPipeline;            // hfe_host.cuh: pinned / device slots and the thread pool of large host calls
 
 struct Model {
@@ -137,6 +152,8 @@ struct Model {
     double svc_guard = 0.0;       // assumed |error| of the float32 SVC decision value
     double gbt_guard = 0.0;       // assumed |error| of the float32 boosted raw score
     ScoreParams base{};           // request fields zero; table pointers filled
+    MmaParams mma{};              // nb > 0: the RBF sum can run on the tensor cores
+    int rbf_engine = 0;           // 0 = automatic (tensor cores when available), 1 = SIMT FFMA2 loop, 2 = tensor cores
     std::vector<void*> allocations;
     uint64_t device_bytes = 0;
     // staging for small host batches (hfe_predict_host with n <= SMALL_HOST_ROWS): allocated once with the model so a
@@ -488,8 +505,74 @@ inline int build_svc(Model* m, const ParsedBlob& pb, uint32_t idx) {
             m->sv_steps = (int)steps;
         }
     }
+    // ---- tensor-core operand image (hfe_mma.cuh) -------------------------------------------------------------------------
+    // t_j = sum_d xc_d W_dj + B_j + r, every number carried as three bfloat16 parts.  Column j of the image is support
+    // vector order[j] (signs alternating, so the float32 partial sums of the epilogue stay small); pad columns have zero
+    // weights and a zero coefficient.
+    std::vector<unsigned char> mma_img;
+    if (n_sv <= MMA_MAX_SV) {
+        MmaParams& Q = m->mma;
+        auto bf16_bits = [](float v) -> uint16_t {              // round to nearest even, like cvt.rn.bf16.f32
+            uint32_t b;
+            std::memcpy(&b, &v, 4);
+            b += 0x7FFFu + ((b >> 16) & 1u);
+            return (uint16_t)(b >> 16);
+        };
+        auto bf16_val = [](uint16_t h) { uint32_t b = (uint32_t)h << 16; float v; std::memcpy(&v, &b, 4); return v; };
+        auto split3 = [&](double v, uint16_t out[3]) {
+            double rest = v;
+            for (int k = 0; k < 3; ++k) {
+                out[k] = bf16_bits((float)rest);
+                rest -= (double)bf16_val(out[k]);
+            }
+        };
+        const int nb = (n_sv + MMA_BLOCK_SV - 1) / MMA_BLOCK_SV, n_pad = nb * MMA_BLOCK_SV;
+        const size_t img_bytes = (size_t)n_pad * MMA_B_CHUNKS * 16;
+        mma_img.assign(img_bytes + (size_t)n_pad * sizeof(float), 0);
+        float* coef_tab = reinterpret_cast<float*>(mma_img.data() + img_bytes);
+        for (int d = 0; d < F; ++d) {
+            Q.center[d] = (float)std::nearbyint(P.mean[d]);
+            Q.dmean[d] = (double)Q.center[d] - P.mean[d];
+            Q.inv_var[d] = 1.0 / (P.scale[d] * P.scale[d]);
+        }
+        Q.neg_c = -P.c_log2;
+        const uint16_t one = bf16_bits(1.f);
+        for (int col = 0; col < n_sv; ++col) {
+            const int j = order[col];
+            const double* s = sv->f64() + (size_t)j * F;
+            uint16_t* row = reinterpret_cast<uint16_t*>(mma_img.data() + (size_t)(col / 8) * (MMA_B_CHUNKS * 128) + (col % 8) * 16);
+            auto at = [&](int chunk, int e) -> uint16_t& { return row[chunk * 64 + e]; };     // chunks are 128 bytes apart
+            double bias = 0.0, ss = 0.0;
+            for (int d = 0; d < F; ++d) {
+                const double w = 2.0 * P.c_log2 * s[d] / P.scale[d];
+                uint16_t p[3];
+                split3(w, p);
+                // feature d sits in chunk d / 8 of its part, element d % 8; parts: hi chunks 0-2, mid 4-6, lo 7-9
+                at(0 + d / 8, d % 8) = p[0];
+                at(4 + d / 8, d % 8) = p[1];
+                at(7 + d / 8, d % 8) = p[2];
+                bias += Q.dmean[d] * w;
+                ss += s[d] * s[d];
+            }
+            bias -= P.c_log2 * ss;
+            uint16_t bp[3];
+            split3(bias, bp);
+            // slot 1 of the third chunk multiplies the constant 1 of the A operand (bias); slots 2-4 select the three parts
+            // of the row term r: its hi part goes to the hi accumulator, mid and lo to the rest accumulator
+            at(2, 1) = bp[0]; at(6, 1) = bp[1]; at(9, 1) = bp[2];
+            at(2, 2) = one;   at(6, 3) = one;   at(6, 4) = one;
+            coef_tab[col] = (float)coef[j];
+        }
+        for (int col = n_sv; col < n_pad; ++col) {                   // pad columns still need the row term (exponent <= 0)
+            uint16_t* row = reinterpret_cast<uint16_t*>(mma_img.data() + (size_t)(col / 8) * (MMA_B_CHUNKS * 128) + (col % 8) * 16);
+            row[2 * 64 + 2] = one; row[6 * 64 + 3] = one; row[6 * 64 + 4] = one;
+        }
+        Q.nb = nb;
+        Q.w_bytes = (int)mma_img.size();
+    }
     std::vector<double> sv_host(sv->f64(), sv->f64() + (size_t)n_sv * F), dual_host(coef, coef + n_sv);
     int rc;
+    if (!mma_img.empty() && (rc = upload(m, mma_img, &m->mma.w_img))) return rc;
     if ((rc = upload(m, tab, &P.sv_tab))) return rc;
     if ((rc = upload(m, sv_host, &P.sv64))) return rc;
     if ((rc = upload(m, dual_host, &P.dual64))) return rc;

@@ -97,6 +97,13 @@ class HFStackB200:
         with open(path, "rb") as fh:
             return cls(fh.read(), device=device)
 
+    def set_rbf_engine(self, engine):
+        """``"auto"`` / ``"simt"`` / ``"tensor"``: what evaluates the RBF sum of the SVC member (both meet the same bars)."""
+        code = {"auto": 0, "simt": 1, "tensor": 2}[engine]
+        capi.check(self._lib.hfe_model_set_rbf_engine(self._handle, code))
+        capi.check(self._lib.hfe_model_get_info(self._handle, C.byref(self.info)))
+        return self
+
     def close(self):
         if getattr(self, "_handle", None) is not None and self._handle:
             self._lib.hfe_model_destroy(self._handle)
