@@ -1,33 +1,34 @@
 // hfe_mma.cuh -- the RBF-SVC member on the 5th-generation tensor cores (tcgen05.mma, accumulators in TMEM).
 //
-// What libsvm computes per row (svm.cpp:461-515, 2821-2904) is f = sum_j coef_j * exp(-gamma |z - s_j|^2) + b, and the
-// exponent is one row of a small dense contraction:
-//     t_j = -c|z - s_j|^2 = sum_d xc_d * W_dj + B_j + r          (log2 units, c = gamma * log2 e)
-//     xc_d = x_d - m_d            raw feature minus a fixed centre (the scaler mean rounded to an integer)
-//     W_dj = 2c s_jd / scale_d    B_j = sum_d (m_d - mean_d) W_dj - c|s_j|^2        r = -c|z|^2   (per row)
-// i.e. T[128 rows x n_sv] = A[128 x K] * Wt[K x n_sv] with the row term and the bias carried in spare K slots.
-// The operands are bfloat16 but nothing is rounded away: every W_dj, B_j and r is split into three bfloat16 parts
-// (hi + mid + lo = 24 significant bits) and so is xc_d; the products of 8-bit significands are exact in the float32
-// accumulator.  For cohorts in the load_data_public.py schema every feature is a small integer, xc_d is one exact
-// bfloat16 and the base block (5 K-steps of 16) is all there is; when a tile holds a value that needs more bits the
-// issuing thread appends the extension block (mid and lo parts of xc, 5 more K-steps) for that tile only.
-// The tensor core aligns the products of one instruction (and the accumulator) to the largest exponent among them and
-// drops what falls below ~2^-24 of it (measured with tools/mma_probe.cu: one term of 144 next to 79 terms of ~1e-4 loses
-// 3e-4).  So terms of different magnitude classes never share an accumulator: per support vector one TMEM column takes
-// the hi x hi products (8-bit x 8-bit significands around 2^3: exact), a second one everything 2^-8 and below (mid and
-// lo parts, extension block); the epilogue adds the two in float32.
+// What libsvm computes per row (svm.cpp:461-515, 2821-2904) is f = sum_j coef_j * exp(-gamma |z - s_j|^2) + b.  With
+// c = gamma * log2 e, a fixed centre m_d (the scaler mean rounded to an integer) and xc_d = x_d - m_d,
+//     exp(-gamma |z - s_j|^2) = 2^(T_j) * 2^(B_j) * 2^(-c|z|^2)
+//     T_j = sum_d xc_d * W_dj,   W_dj = 2c s_jd / scale_d,   B_j = sum_d (m_d - mean_d) W_dj - c|s_j|^2
+// so the exponents of one tile are a small dense contraction T[128 rows x n_sv] = A[128 x K] * W[K x n_sv]; 2^(B_j) is
+// folded into the coefficient and the row factor is applied once, in float64, to the finished sum.
+// The operands are bfloat16 but nothing is rounded away: every W_dj is split into three bfloat16 parts (hi + mid + lo =
+// 24 significant bits) and so is xc_d; products of 8-bit significands are exact in the float32 accumulator.  For
+// cohorts in the load_data_public.py schema every feature is a small integer, xc_d is one exact bfloat16 and the base
+// block (5 K-steps of 16) is all there is; when a tile holds a value that needs more bits the issuing thread puts the
+// extension block (mid and lo parts of xc, 5 more K-steps) in front of it for that tile only.
+// The tensor core aligns the products of one instruction and the accumulator to the largest exponent among them and
+// drops what falls below ~2^-24 of it (measured with tools/mma_probe.cu).  Hence: the large constant terms (B_j, the
+// row term) stay out of the accumulator, and K-steps run from the smallest parts to the largest, so each accumulation
+// loses at most the float32 rounding of the exponent itself.
 //
 // One persistent CTA per SM, 14 warps:
-//   warps 0-3   producers: load the tile's 128 rows (coalesced column reads), centre and split them, write the A operand
-//               into shared memory in the canonical K-major core-matrix layout; they also evaluate the tree and logistic
-//               members (their share of the combiner's logit travels to the epilogue through shared memory)
-//   warps 4-7   epilogue of stream 0, warps 8-11 epilogue of stream 1: thread = row (TMEM lane); tcgen05.ld 16 columns
-//               at a time, ex2, coefficient FFMA2, float64 fold; then Platt + coupling + combiner (finish_rows_fast)
+//   warps 0-3   producers: load the tile's 128 rows (coalesced column reads, the next tile's loads in flight while this
+//               one is processed), centre and split them, write the A operand into shared memory in the canonical
+//               K-major core-matrix layout, evaluate the tree and logistic members; a few tiles later, when the RBF sums
+//               of a tile have come back through shared memory, the same thread finishes its row: Platt + coupling +
+//               combiner (finish_rows_fast), four tiles at a time so that four float64 chains are interleaved
+//   warps 4-7   exponent warps of stream 0, warps 8-11 of stream 1: thread = row (TMEM lane); tcgen05.ld 16 columns at a
+//               time, ex2, coefficient FFMA2, float64 fold -- nothing else, so that the MUFU pipe always has work
 //   warps 12,13 one lane each issues the tcgen05.mma instructions of its stream and commits them to mbarriers
-// Tiles alternate between the two streams.  Support vectors are taken in blocks of 64; TMEM (512 columns) is cut into
-// four regions of 128 columns ([hi accumulator | rest accumulator] of one block), two per stream: while a stream's
-// epilogue warps drain one block from one region, the tensor core fills the other, and the other stream's epilogue
-// keeps the MUFU pipe busy in the meantime.
+// Tiles alternate between the two streams.  Support vectors are taken in blocks of up to 128; TMEM (512 columns) is cut
+// into four regions, two per stream: while a stream's epilogue warps drain one block from one region the tensor core
+// fills the other, and the other stream keeps the MUFU pipe busy in the meantime.  Both the MUFU pipe and the TMEM read
+// path move 16 values per clock and SM: 28 clocks per row for 448 support vectors is the floor of this design.
 #pragma once
 
 #include <cuda_bf16.h>
@@ -37,12 +38,17 @@
 namespace hfe {
 
 constexpr int MMA_TILE_ROWS = 128;
-constexpr int MMA_PRODUCER_WARPS = 4, MMA_EPI_WARPS = 8, MMA_ISSUE_WARPS = 2;
-constexpr int MMA_THREADS = 32 * (MMA_PRODUCER_WARPS + MMA_EPI_WARPS + MMA_ISSUE_WARPS);      // 448
+constexpr int MMA_PRODUCER_WARPS = 4, MMA_FINISH_WARPS = 2, MMA_EPI_WARPS = 8, MMA_ISSUE_WARPS = 2;
+constexpr int MMA_EPI_WARP0 = MMA_PRODUCER_WARPS + MMA_FINISH_WARPS;             // 6: exponent warps 6..13
+constexpr int MMA_ISSUE_WARP0 = MMA_EPI_WARP0 + MMA_EPI_WARPS;                   // 14, 15
+constexpr int MMA_THREADS = 32 * (MMA_PRODUCER_WARPS + MMA_FINISH_WARPS + MMA_EPI_WARPS + MMA_ISSUE_WARPS);   // 512
 constexpr int MMA_A_STAGES = 3;
 constexpr int MMA_A_CHUNKS = 20;                         // 16-byte K chunks per row: 10 base + 10 extension
 constexpr int MMA_A_STAGE_BYTES = (MMA_TILE_ROWS / 8) * MMA_A_CHUNKS * 128;                   // 40 960
-constexpr int MMA_SIDE_BYTES = MMA_TILE_ROWS * 32;       // per (stream, slot): zpart, p_gbt, p_lin, flags per row
+constexpr int MMA_RING = 8;                              // tiles between a row's production and its float64 epilogue
+constexpr int MMA_RING_SLOT_BYTES = MMA_TILE_ROWS * 20;  // per tile and row: RBF sum (f64), logistic dot, stump score, gamma|z|^2 (f32)
+constexpr int MMA_REGION_COLS = 128;                     // TMEM columns per region
+constexpr int MMA_TAIL_ROWS = 4;                         // tiles whose float64 epilogue one thread runs interleaved
 
 // ---- PTX helpers ---------------------------------------------------------------------------------------------------------
 __device__ __forceinline__ unsigned smem_addr(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
@@ -106,15 +112,6 @@ __device__ __forceinline__ void tmem_ld_wait(unsigned (&v)[16]) {
                  :: "memory");
 }
 
-__device__ __forceinline__ void tmem_ld_wait2(unsigned (&v)[16], unsigned (&w)[16]) {
-    asm volatile("tcgen05.wait::ld.sync.aligned;"
-                 : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]),
-                   "+r"(v[8]), "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15])
-                 :: "memory");
-    asm volatile("" : "+r"(w[0]), "+r"(w[1]), "+r"(w[2]), "+r"(w[3]), "+r"(w[4]), "+r"(w[5]), "+r"(w[6]), "+r"(w[7]),
-                      "+r"(w[8]), "+r"(w[9]), "+r"(w[10]), "+r"(w[11]), "+r"(w[12]), "+r"(w[13]), "+r"(w[14]), "+r"(w[15]));
-}
-
 __device__ __forceinline__ unsigned pack_bf16(float lo, float hi) {       // lo in bits [0,16), hi in [16,32)
     __nv_bfloat162 p = __floats2bfloat162_rn(lo, hi);
     return *reinterpret_cast<unsigned*>(&p);
@@ -128,46 +125,53 @@ __device__ __forceinline__ double widen_f32(float v) {
     return __hiloint2double((int)((b & 0x80000000u) | (((b & 0x7FFFFFFFu) >> 3) + 0x38000000u)), (int)(b << 29));
 }
 
+// (hi, lo) += v without rounding error (Knuth's TwoSum; lo collects what hi cannot hold)
+__device__ __forceinline__ void two_sum_add(float& hi, float& lo, float v) {
+    const float s = __fadd_rn(hi, v);
+    const float z = __fsub_rn(s, hi);
+    lo = __fadd_rn(lo, __fadd_rn(__fsub_rn(hi, __fsub_rn(s, z)), __fsub_rn(v, z)));
+    hi = s;
+}
+
 // ---- the kernel ------------------------------------------------------------------------------------------------------------
 template <int TREE_MODE>
 __global__ void __launch_bounds__(MMA_THREADS, 1)
 hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ MmaParams Q) {
     static_assert(TREE_MODE == 0 || TREE_MODE == 1, "general tree tables keep the SIMT kernel");
     extern __shared__ __align__(1024) unsigned char smem[];
-    // [W image + coef | A stages | side data | barriers]
+    // [W image + coef | A stages | ring: sums, logit shares, gamma|z|^2 | barriers]
     const int w_region = (Q.w_bytes + 1023) & ~1023;
     unsigned char* s_w = smem;
     unsigned char* s_a = smem + w_region;
-    unsigned char* s_side = s_a + MMA_A_STAGES * MMA_A_STAGE_BYTES;
-    unsigned long long* s_bar = reinterpret_cast<unsigned long long*>(s_side + 4 * MMA_SIDE_BYTES);
+    unsigned char* s_ring = s_a + MMA_A_STAGES * MMA_A_STAGE_BYTES;
+    unsigned long long* s_bar = reinterpret_cast<unsigned long long*>(s_ring + MMA_RING * MMA_RING_SLOT_BYTES);
     unsigned* s_misc = reinterpret_cast<unsigned*>(s_bar + 32);
-    // barrier indices
-    enum { B_W = 0, B_AFULL = 1, B_AEMPTY = 4, B_ACCFULL = 7, B_ACCEMPTY = 11, B_SIDEFULL = 15, B_SIDEEMPTY = 19, B_COUNT = 23 };
+    enum { B_W = 0, B_AFULL = 1, B_AEMPTY = 4, B_ACCFULL = 7, B_ACCEMPTY = 11, B_SUMFULL = 15, B_RINGFREE = 23 };
     auto bar = [&](int i) { return smem_addr(s_bar + i); };
+    auto ring_sum = [&](int slot) { return reinterpret_cast<double*>(s_ring + slot * MMA_RING_SLOT_BYTES); };
+    auto ring_lin = [&](int slot) { return reinterpret_cast<float*>(s_ring + slot * MMA_RING_SLOT_BYTES + MMA_TILE_ROWS * 8); };
+    auto ring_raw = [&](int slot) { return reinterpret_cast<float*>(s_ring + slot * MMA_RING_SLOT_BYTES + MMA_TILE_ROWS * 12); };
+    auto ring_gzz = [&](int slot) { return reinterpret_cast<float*>(s_ring + slot * MMA_RING_SLOT_BYTES + MMA_TILE_ROWS * 16); };
     volatile unsigned* s_tmem = s_misc;                    // TMEM base address
     volatile unsigned* s_ext = s_misc + 4;                 // [stage][producer warp]: tile needs the extension block
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const long long n_tiles = (P.n + MMA_TILE_ROWS - 1) / MMA_TILE_ROWS;
-    const int nb = Q.nb;
+    const int nb = Q.nb, bsv = Q.block_sv;
 
     // ---- set-up -------------------------------------------------------------------------------------------------------------
-    {   // zero the A stages once: the padding chunk of every K block is never written again
+    {   // zero the A stages once: the padding chunk of each K block is never written again
         uint4* z = reinterpret_cast<uint4*>(s_a);
         for (int i = tid; i < MMA_A_STAGES * MMA_A_STAGE_BYTES / 16; i += MMA_THREADS) z[i] = make_uint4(0, 0, 0, 0);
     }
     if (tid == 0) {
         mbar_init(bar(B_W), 1);
-        for (int i = 0; i < MMA_A_STAGES; ++i) { mbar_init(bar(B_AFULL + i), MMA_PRODUCER_WARPS); mbar_init(bar(B_AEMPTY + i), 1); }
-        for (int i = 0; i < 4; ++i) {
-            mbar_init(bar(B_ACCFULL + i), 1);
-            mbar_init(bar(B_ACCEMPTY + i), 4);
-            mbar_init(bar(B_SIDEFULL + i), MMA_PRODUCER_WARPS);
-            mbar_init(bar(B_SIDEEMPTY + i), 4);
-        }
+        for (int i = 0; i < MMA_A_STAGES; ++i) { mbar_init(bar(B_AFULL + i), 4); mbar_init(bar(B_AEMPTY + i), 1); }
+        for (int i = 0; i < 4; ++i) { mbar_init(bar(B_ACCFULL + i), 1); mbar_init(bar(B_ACCEMPTY + i), 4); }
+        for (int i = 0; i < MMA_RING; ++i) { mbar_init(bar(B_SUMFULL + i), 4); mbar_init(bar(B_RINGFREE + i), MMA_FINISH_WARPS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 12) {
+    if (warp == MMA_ISSUE_WARP0) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_addr((const void*)s_tmem)), "r"(512));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
     }
@@ -184,51 +188,69 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
     }
 
     if (warp < MMA_PRODUCER_WARPS) {
-        // =========================== producers ==================================================================================
+        // =========================== producers ====================================================================================
         const bool has_lin = P.slot_lin >= 0;
+        const int prow = tid;                                  // this thread's row of every tile
+        auto fetch = [&](long long tile, float (&x)[F]) {
+            // this row's 17 features: one coalesced 128-byte read per warp and column, all in flight at once
+            const long long row = tile * MMA_TILE_ROWS + prow;
+            const long long row_ld = row < P.n ? row : 0;
+#pragma unroll
+            for (int f = 0; f < F; ++f) x[f] = __ldg(P.x + P.col_off[f] + row_ld);
+            if (P.perm_col >= 0) {                             // a permutation-importance pass: one column through the index
+                const int src = __ldg(P.perm_idx + row_ld);
+                HFE_ASSERT_IN(src >= 0 && src < P.n);
+#pragma unroll
+                for (int f = 0; f < F; ++f)
+                    if (f == P.perm_col) x[f] = __ldg(P.x + P.col_off[f] + src);
+            }
+        };
+        float xn[F];
+        if ((long long)blockIdx.x < n_tiles) fetch(blockIdx.x, xn);
         long long i = 0;
         for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++i) {
             const int stage = (int)(i % MMA_A_STAGES);
-            const int s = (int)(i & 1), slot = (int)((i >> 1) & 1);
-            const long long row = tile * MMA_TILE_ROWS + tid;
+            const long long row = tile * MMA_TILE_ROWS + prow;
             const bool valid = row < P.n;
-            const long long row_ld = valid ? row : 0;
-            // this row's 17 features: one coalesced 128-byte read per warp and column, all in flight at once
             float x[F];
 #pragma unroll
-            for (int f = 0; f < F; ++f) x[f] = __ldg(P.x + P.col_off[f] + row_ld);
-            if (P.perm_col >= 0) {
-                HFE_ASSERT_IN(__ldg(P.perm_idx + row_ld) >= 0 && __ldg(P.perm_idx + row_ld) < P.n);
-#pragma unroll
-                for (int f = 0; f < F; ++f)
-                    if (f == P.perm_col) x[f] = __ldg(P.x + P.col_off[f] + __ldg(P.perm_idx + row_ld));
-            }
+            for (int f = 0; f < F; ++f) x[f] = xn[f];
+            if (tile + gridDim.x < n_tiles) fetch(tile + gridDim.x, xn);       // in flight while this tile is processed
             float probe = 0.f;
 #pragma unroll
             for (int f = 0; f < F; ++f) probe = fmaf(x[f], 0.f, probe);          // NaN exactly when some x is NaN / Inf
             const bool nonfinite = valid && !(probe == 0.f);
-            if (!valid || nonfinite) {
-#pragma unroll
-                for (int f = 0; f < F; ++f) x[f] = Q.center[f];                      // keeps NaN out of the tensor core
-            }
-            // centre, split, row term
-            float xc[F], hi[F], rem[F];
-            double zz = 0.0, zl = P.lin_intercept;
-            bool inexact = false;
+            // centre; |z|^2 as sum_d xc (a xc + b) + c; the exponent of no support vector may leave the float32 2^x range:
+            // |T_j| <= max |W| * sum_d |xc_d|
+            float xc[F], sum_abs = 0.f, zz = Q.zz_c;
 #pragma unroll
             for (int f = 0; f < F; ++f) {
                 xc[f] = x[f] - Q.center[f];
-                hi[f] = bf16_round(xc[f]);
-                rem[f] = xc[f] - hi[f];
-                inexact = inexact || (rem[f] != 0.f);
-                const double zd = (double)xc[f] + Q.dmean[f];
-                zz = fma(zd * zd, Q.inv_var[f], zz);
-                if (has_lin) zl = fma((double)x[f], P.lin_coef[f], zl);
+                sum_abs += fabsf(xc[f]);
+                zz = fmaf(xc[f], fmaf(Q.zz_a[f], xc[f], Q.zz_b[f]), zz);
             }
-            const float r = (float)(Q.neg_c * zz);
-            const float r_hi = bf16_round(r), r_mid = bf16_round(r - r_hi), r_lo = bf16_round((r - r_hi) - r_mid);
-            // the other members (their links, and their share of the combiner's logit)
-            double raw1[1] = {0.0}, zl1[1] = {zl}, zpart[1], member[3][1];
+            const bool fix_row = valid && (nonfinite || !(sum_abs * Q.wmax_all <= 96.f));
+            const bool keep = valid && !fix_row;
+            // bfloat16 hi parts, two features per conversion; what one bfloat16 cannot carry stays in rem
+            unsigned hp[9];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) hp[k] = pack_bf16(xc[2 * k], xc[2 * k + 1]);
+            hp[8] = pack_bf16(xc[16], 0.f);
+            float rem[F];
+            unsigned rem_bits = 0;
+#pragma unroll
+            for (int f = 0; f < F; ++f) {
+                const float hi = __uint_as_float((f & 1) ? (hp[f >> 1] & 0xFFFF0000u) : (hp[f >> 1] << 16));
+                rem[f] = xc[f] - hi;
+                rem_bits |= __float_as_uint(rem[f]);
+            }
+            const bool inexact = keep && (rem_bits << 1) != 0;
+            if (!keep) {                                   // keeps NaN / Inf (and rows beyond n) out of the tensor core
+#pragma unroll
+                for (int k = 0; k < 9; ++k) hp[k] = 0u;
+            }
+            // boosted stumps: the raw score goes to the thread's later self through the ring, links are evaluated there
+            float raw32 = 0.f;
             if (TREE_MODE == 1) {
                 float acc[1] = {0.f};
 #pragma unroll
@@ -236,25 +258,34 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
                     const float xf[1] = {x[f]};
                     apply_splits<1>(P, f, xf, acc);
                 }
-                raw1[0] = P.gbt_split_base + (double)acc[0];
+                raw32 = acc[0];
             }
-            partial_logit_fast<1>(P, TREE_MODE != 0, has_lin, raw1, zl1, zpart, member);
+            if (nonfinite) atomicOr(P.status, HFE_ROW_NONFINITE);
+            // what the finishing warps need besides the RBF sum (they have released slot i % 8 of the ring after tile i - 8)
+            mbar_wait(bar(B_RINGFREE + (int)(i % MMA_RING)), (unsigned)(((i / MMA_RING) & 1) ^ 1));
+            ring_raw((int)(i % MMA_RING))[prow] = raw32;
+            ring_gzz((int)(i % MMA_RING))[prow] = fix_row ? -1.f : (float)P.gamma * zz;
 
             mbar_wait(bar(B_AEMPTY + stage), (unsigned)(((i / MMA_A_STAGES) & 1) ^ 1));
-            // A operand: [row group][chunk][row in group][8 bf16]; base chunks H0 H1 H2 0 | H0 H1 H2 H0 H1 H2 (chunk 3 stays 0):
-            // K-steps 0,1 meet the hi parts of W (-> hi accumulator), K-steps 2-4 the mid and lo parts (-> rest accumulator)
-            unsigned char* a_row = s_a + stage * MMA_A_STAGE_BYTES + (tid >> 3) * (MMA_A_CHUNKS * 128) + (tid & 7) * 16;
-            const uint4 h0 = make_uint4(pack_bf16(hi[0], hi[1]), pack_bf16(hi[2], hi[3]), pack_bf16(hi[4], hi[5]), pack_bf16(hi[6], hi[7]));
-            const uint4 h1 = make_uint4(pack_bf16(hi[8], hi[9]), pack_bf16(hi[10], hi[11]), pack_bf16(hi[12], hi[13]), pack_bf16(hi[14], hi[15]));
-            const uint4 h2 = make_uint4(pack_bf16(hi[16], 1.f), pack_bf16(r_hi, r_mid), pack_bf16(r_lo, 0.f), 0u);
-            *reinterpret_cast<uint4*>(a_row + 0 * 128) = h0; *reinterpret_cast<uint4*>(a_row + 1 * 128) = h1;
-            *reinterpret_cast<uint4*>(a_row + 2 * 128) = h2;
-            *reinterpret_cast<uint4*>(a_row + 4 * 128) = h0; *reinterpret_cast<uint4*>(a_row + 5 * 128) = h1;
-            *reinterpret_cast<uint4*>(a_row + 6 * 128) = h2; *reinterpret_cast<uint4*>(a_row + 7 * 128) = h0;
-            *reinterpret_cast<uint4*>(a_row + 8 * 128) = h1; *reinterpret_cast<uint4*>(a_row + 9 * 128) = h2;
-            // extension block M0 M1 M2 M0 M1 M2 L0 L1 L2: only tiles holding a value that one bfloat16 cannot carry use it,
-            // but then all four warps' rows must be there
+            // A operand: [row group][chunk][row in group][8 bf16]; base chunks H0 H1 H2 H0 H1 H2 H0 H1 H2 0 meet the lo, mid and
+            // hi parts of W in that order (chunk 9 stays zero)
+            unsigned char* a_row = s_a + stage * MMA_A_STAGE_BYTES + (prow >> 3) * (MMA_A_CHUNKS * 128) + (prow & 7) * 16;
+            const uint4 h0 = make_uint4(hp[0], hp[1], hp[2], hp[3]);
+            const uint4 h1 = make_uint4(hp[4], hp[5], hp[6], hp[7]);
+            const uint4 h2 = make_uint4(hp[8], 0u, 0u, 0u);
+#pragma unroll
+            for (int rep = 0; rep < 3; ++rep) {
+                *reinterpret_cast<uint4*>(a_row + (3 * rep + 0) * 128) = h0;
+                *reinterpret_cast<uint4*>(a_row + (3 * rep + 1) * 128) = h1;
+                *reinterpret_cast<uint4*>(a_row + (3 * rep + 2) * 128) = h2;
+            }
+            // extension chunks L0 L1 M0 L2 M1 M2 M0 M1 M2 0 (mid and lo parts of the centred features): only tiles holding a value
+            // that one bfloat16 cannot carry use them, but then the rows of all four warps must be there
             const bool ext = __any_sync(0xFFFFFFFFu, inexact);
+            if (!keep) {
+#pragma unroll
+                for (int f = 0; f < F; ++f) rem[f] = 0.f;
+            }
             uint4 m0 = make_uint4(0, 0, 0, 0), m1 = m0, m2 = m0, l0 = m0, l1 = m0, l2 = m0;
             if (ext) {
                 float mid[F], lo[F];
@@ -268,135 +299,162 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
                 l2 = make_uint4(pack_bf16(lo[16], 0.f), 0u, 0u, 0u);
             }
             unsigned char* e_row = a_row + 10 * 128;
-            *reinterpret_cast<uint4*>(e_row + 0 * 128) = m0; *reinterpret_cast<uint4*>(e_row + 1 * 128) = m1;
-            *reinterpret_cast<uint4*>(e_row + 2 * 128) = m2; *reinterpret_cast<uint4*>(e_row + 3 * 128) = m0;
+            *reinterpret_cast<uint4*>(e_row + 0 * 128) = l0; *reinterpret_cast<uint4*>(e_row + 1 * 128) = l1;
+            *reinterpret_cast<uint4*>(e_row + 2 * 128) = m0; *reinterpret_cast<uint4*>(e_row + 3 * 128) = l2;
             *reinterpret_cast<uint4*>(e_row + 4 * 128) = m1; *reinterpret_cast<uint4*>(e_row + 5 * 128) = m2;
-            *reinterpret_cast<uint4*>(e_row + 6 * 128) = l0; *reinterpret_cast<uint4*>(e_row + 7 * 128) = l1;
-            *reinterpret_cast<uint4*>(e_row + 8 * 128) = l2;
+            *reinterpret_cast<uint4*>(e_row + 6 * 128) = m0; *reinterpret_cast<uint4*>(e_row + 7 * 128) = m1;
+            *reinterpret_cast<uint4*>(e_row + 8 * 128) = m2;
             if (lane == 0) s_ext[stage * 4 + warp] = ext ? 1u : 0u;
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");           // these stores before the tensor core's reads
             __syncwarp();
             if (lane == 0) mbar_arrive(bar(B_AFULL + stage));
 
-            // side data for the epilogue thread of this row
-            mbar_wait(bar(B_SIDEEMPTY + 2 * s + slot), (unsigned)(((i >> 2) & 1) ^ 1));
-            double* side = reinterpret_cast<double*>(s_side + (2 * s + slot) * MMA_SIDE_BYTES) + tid * 4;
-            side[0] = zpart[0];
-            side[1] = member[1][0];
-            side[2] = member[2][0];
-            side[3] = nonfinite ? 1.0 : 0.0;
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bar(B_SIDEFULL + 2 * s + slot));
         }
         // the last commits onto the A-stage barriers must have landed before the CTA may retire
         for (long long k = (i > MMA_A_STAGES ? i - MMA_A_STAGES : 0); k < i; ++k)
             mbar_wait(bar(B_AEMPTY + (int)(k % MMA_A_STAGES)), (unsigned)((k / MMA_A_STAGES) & 1));
-    } else if (warp < MMA_PRODUCER_WARPS + MMA_EPI_WARPS) {
-        // =========================== epilogue warps ==============================================================================
-        const int s = (warp - MMA_PRODUCER_WARPS) >> 2;              // stream
+    } else if (warp < MMA_EPI_WARP0) {
+        // =========================== finishing warps: the float64 epilogue of every row ===========================================
+        // 64 threads; thread t finishes rows t and t + 64 of two consecutive tiles at a time, so four independent float64
+        // chains (Platt, clamp, coupling, links, combiner: the SIMT kernel's epilogue code) are interleaved
+        constexpr int R = MMA_TAIL_ROWS;
+        const bool has_lin = P.slot_lin >= 0;
+        const int frow = tid - 32 * MMA_PRODUCER_WARPS;        // 0..63
+        const long long my_tiles = (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x;
+        for (long long t0 = 0; t0 < my_tiles; t0 += 2) {
+            const int count = my_tiles - t0 >= 2 ? 2 : 1;
+            double f_svc[R], zpart[R], p1[R], zfin[R], p_svc[R], raw[R], zl[R], member[3][R];
+            float gzz[R];
+            long long rows[R];
+            bool unc[R];
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const long long t = t0 + (r >> 1);
+                const int prow = frow + 64 * (r & 1);
+                rows[r] = P.n;
+                f_svc[r] = P.svc_intercept;
+                raw[r] = zl[r] = 0.0;
+                gzz[r] = 0.f;
+                if ((r >> 1) < count) {
+                    const int slot = (int)(t % MMA_RING);
+                    mbar_wait(bar(B_SUMFULL + slot), (unsigned)((t / MMA_RING) & 1));
+                    rows[r] = ((long long)blockIdx.x + t * gridDim.x) * MMA_TILE_ROWS + prow;
+                    gzz[r] = ring_gzz(slot)[prow];
+                    raw[r] = P.gbt_split_base + (double)ring_raw(slot)[prow];
+                    zl[r] = Q.lin_base + (double)ring_lin(slot)[prow];      // logistic member: the dot product came off the tensor core
+                    f_svc[r] = fma(ring_sum(slot)[prow], exp_neg_fast(-(double)fmaxf(gzz[r], 0.f)), P.svc_intercept);
+                }
+            }
+            __syncwarp();
+            if (lane == 0) {                                    // the ring slots may be rewritten
+                mbar_arrive(bar(B_RINGFREE + (int)(t0 % MMA_RING)));
+                if (count == 2) mbar_arrive(bar(B_RINGFREE + (int)((t0 + 1) % MMA_RING)));
+            }
+            partial_logit_fast<R>(P, TREE_MODE != 0, has_lin, raw, zl, zpart, member);
+            finish_rows_fast<R>(P, true, f_svc, zpart, p1, zfin, p_svc, unc);
+            unsigned hits = 0;
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const long long row = rows[r];
+                const bool valid = row < P.n;
+                const unsigned char lab = zfin[r] > 0 ? 1 : 0;
+                const bool fix = valid && (unc[r] || gzz[r] < 0.f);
+                if (valid) {
+                    if (P.out) *reinterpret_cast<float2*>(P.out + 2 * row) = make_float2((float)(1.0 - p1[r]), (float)p1[r]);
+                    if (P.out64) { P.out64[2 * row] = 1.0 - p1[r]; P.out64[2 * row + 1] = p1[r]; }
+                    if (P.labels) P.labels[row] = lab;
+                    if (P.decision) P.decision[row] = zfin[r];
+                    if (P.meta) {
+                        P.meta[row * P.n_members + P.slot_svc] = p_svc[r];
+                        if (P.slot_gbt >= 0) P.meta[row * P.n_members + P.slot_gbt] = member[1][r];
+                        if (P.slot_lin >= 0) P.meta[row * P.n_members + P.slot_lin] = member[2][r];
+                    }
+                }
+                if (fix) {      // result hinges on a branch (or the row could not be scored here): the float64 fix-up redoes it
+                    const unsigned at = atomicAdd(P.status + HFE_STATUS_LIST_LEN, 1u);
+                    if (at < (unsigned)HFE_WORKLIST_CAPACITY) P.status[HFE_STATUS_HEADER_WORDS + at] = (unsigned)row;
+                    else atomicOr(P.status, HFE_WORKLIST_OVERFLOW);
+                }
+                if (P.y && P.score) hits += (valid && !fix && lab == P.y[row]) ? 1u : 0u;
+            }
+            if (P.y && P.score) {                                       // accuracy count; flagged rows are counted by the fix-up
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) hits += __shfl_down_sync(0xFFFFFFFFu, hits, o);
+                if (lane == 0 && hits) atomicAdd(P.score, (unsigned long long)hits);
+            }
+        }
+    } else if (warp < MMA_ISSUE_WARP0) {
+        // =========================== exponent warps ================================================================================
+        const int s = (warp - MMA_EPI_WARP0) >> 2;                   // stream
         const int row_in_tile = (warp & 3) * 32 + lane;              // TMEM lane = row of the tile (warp % 4 picks the lane quarter)
         const unsigned lane_base = tmem_base + ((unsigned)((warp & 3) * 32) << 16);
         mbar_wait(bar(B_W), 0);
-        const float* s_coef = reinterpret_cast<const float*>(s_w + (size_t)nb * MMA_BLOCK_SV * (MMA_B_CHUNKS * 16));
+        const float* s_coef = reinterpret_cast<const float*>(s_w + (size_t)nb * bsv * (MMA_B_CHUNKS * 16));
+        const int steps = bsv >> 4;
         long long j = 0;
         for (long long i = s, tile = blockIdx.x + (long long)s * gridDim.x; tile < n_tiles; i += 2, tile += 2LL * gridDim.x, ++j) {
-            const int slot = (int)(j & 1);
-            mbar_wait(bar(B_SIDEFULL + 2 * s + slot), (unsigned)((j >> 1) & 1));
-            const double* side = reinterpret_cast<const double*>(s_side + (2 * s + slot) * MMA_SIDE_BYTES) + row_in_tile * 4;
-            const double zpart0 = side[0], p_gbt = side[1], p_lin = side[2];
-            const bool nonfinite = side[3] != 0.0;
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bar(B_SIDEEMPTY + 2 * s + slot));
-
-            double acc64 = 0.0;
+            float acc_hi = 0.f, acc_lo = 0.f; // two-float accumulator (error-free TwoSum): keeps the float64 pipe out of the hot loop
+            unsigned lin_dot = 0;             // last column of the last block: x . (logistic coefficients), not an exponent
 #pragma unroll 1
             for (int blk = 0; blk < nb; ++blk) {
                 const long long use = j * nb + blk;                  // this stream's running count of blocks
                 const int reg = (int)(use & 1);
                 mbar_wait(bar(B_ACCFULL + 2 * s + reg), (unsigned)((use >> 1) & 1));
                 tc_fence_after();
-                const unsigned taddr = lane_base + (unsigned)((2 * s + reg) * (2 * MMA_BLOCK_SV));   // hi accumulator; rest at +64
-                const float4* coef4 = reinterpret_cast<const float4*>(s_coef + blk * MMA_BLOCK_SV);
-                // 16 support vectors per step: exponent = hi + rest, 2^x on the MUFU pipe, coefficient FFMA2 (two vectors per
-                // instruction), float32 partial sums of 4 vectors each folded into the float64 accumulator; the TMEM loads of
-                // the next step are in flight while this one is consumed
-                unsigned ha[16], ra[16], hb[16], rb[16];
-                tmem_ld16(taddr, ha);
-                tmem_ld16(taddr + MMA_BLOCK_SV, ra);
-                auto consume = [&](const unsigned (&h)[16], const unsigned (&r)[16], int c0) {
+                const unsigned taddr = lane_base + (unsigned)((2 * s + reg) * MMA_REGION_COLS);
+                const float4* coef4 = reinterpret_cast<const float4*>(s_coef + blk * bsv);
+                // 16 support vectors per step: 2^T on the MUFU pipe, coefficient FFMA2 (two vectors per instruction), float32
+                // partial sums of 4 vectors each folded into the float64 accumulator; the TMEM load of the next step is in
+                // flight while this one is consumed
+                unsigned va[16], vb[16];
+                auto consume = [&](const unsigned (&v)[16], const float4* cp) {
                     float2 a0 = make_float2(0.f, 0.f), a1 = a0;
 #pragma unroll
                     for (int k = 0; k < 4; ++k) {
-                        const float4 c = coef4[(c0 >> 2) + k];
-                        const float2 t0 = __fadd2_rn(make_float2(__uint_as_float(h[4 * k]), __uint_as_float(h[4 * k + 1])),
-                                                     make_float2(__uint_as_float(r[4 * k]), __uint_as_float(r[4 * k + 1])));
-                        const float2 t1 = __fadd2_rn(make_float2(__uint_as_float(h[4 * k + 2]), __uint_as_float(h[4 * k + 3])),
-                                                     make_float2(__uint_as_float(r[4 * k + 2]), __uint_as_float(r[4 * k + 3])));
-                        a0 = __ffma2_rn(make_float2(ex2_approx(t0.x), ex2_approx(t0.y)), make_float2(c.x, c.y), a0);
-                        a1 = __ffma2_rn(make_float2(ex2_approx(t1.x), ex2_approx(t1.y)), make_float2(c.z, c.w), a1);
+                        const float4 c = cp[k];
+                        const float2 e0 = make_float2(ex2_approx(__uint_as_float(v[4 * k])), ex2_approx(__uint_as_float(v[4 * k + 1])));
+                        const float2 e1 = make_float2(ex2_approx(__uint_as_float(v[4 * k + 2])), ex2_approx(__uint_as_float(v[4 * k + 3])));
+                        a0 = __ffma2_rn(e0, make_float2(c.x, c.y), a0);
+                        a1 = __ffma2_rn(e1, make_float2(c.z, c.w), a1);
                     }
-                    acc64 += widen_f32((a0.x + a0.y) + (a1.x + a1.y));
+                    two_sum_add(acc_hi, acc_lo, (a0.x + a0.y) + (a1.x + a1.y));
                 };
-#pragma unroll
-                for (int c0 = 0; c0 < MMA_BLOCK_SV; c0 += 32) {
-                    tmem_ld_wait2(ha, ra);
-                    tmem_ld16(taddr + c0 + 16, hb);
-                    tmem_ld16(taddr + MMA_BLOCK_SV + c0 + 16, rb);
-                    consume(ha, ra, c0);
-                    tmem_ld_wait2(hb, rb);
-                    if (c0 + 32 < MMA_BLOCK_SV) {
-                        tmem_ld16(taddr + c0 + 32, ha);
-                        tmem_ld16(taddr + MMA_BLOCK_SV + c0 + 32, ra);
-                    }
-                    consume(hb, rb, c0 + 16);
+                tmem_ld16(taddr, va);
+                int st = 0;
+#pragma unroll 1
+                for (; st + 2 <= steps; st += 2) {
+                    tmem_ld_wait(va);
+                    tmem_ld16(taddr + (st + 1) * 16, vb);
+                    consume(va, coef4 + st * 4);
+                    tmem_ld_wait(vb);
+                    if (st + 2 < steps) tmem_ld16(taddr + (st + 2) * 16, va);
+                    consume(vb, coef4 + (st + 1) * 4);
+                }
+                if (st < steps) {
+                    tmem_ld_wait(va);
+                    consume(va, coef4 + st * 4);
+                    lin_dot = va[15];
+                } else {
+                    lin_dot = vb[15];
                 }
                 // this region may be overwritten by the MMAs of the block after next
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(bar(B_ACCEMPTY + 2 * s + reg));
             }
-
-            // ---- float64 epilogue of this row: Platt, clamp, coupling, combiner (the same code as the SIMT kernel) --------
-            const long long row = tile * MMA_TILE_ROWS + row_in_tile;
-            const double f_svc[1] = {acc64 + P.svc_intercept};
-            const double zp[1] = {zpart0};
-            double p1[1], zfin[1], p_svc[1];
-            bool unc[1];
-            finish_rows_fast<1>(P, true, f_svc, zp, p1, zfin, p_svc, unc);
-            const bool valid = row < P.n;
-            const unsigned char lab = zfin[0] > 0 ? 1 : 0;
-            const bool fix = valid && (unc[0] || nonfinite);
-            if (valid) {
-                if (P.out) *reinterpret_cast<float2*>(P.out + 2 * row) = make_float2((float)(1.0 - p1[0]), (float)p1[0]);
-                if (P.out64) { P.out64[2 * row] = 1.0 - p1[0]; P.out64[2 * row + 1] = p1[0]; }
-                if (P.labels) P.labels[row] = lab;
-                if (P.decision) P.decision[row] = zfin[0];
-                if (P.meta) {
-                    P.meta[row * P.n_members + P.slot_svc] = p_svc[0];
-                    if (P.slot_gbt >= 0) P.meta[row * P.n_members + P.slot_gbt] = p_gbt;
-                    if (P.slot_lin >= 0) P.meta[row * P.n_members + P.slot_lin] = p_lin;
-                }
-            }
-            if (fix) {          // result hinges on a branch (or the row is not finite): the float64 fix-up kernel redoes it
-                const unsigned at = atomicAdd(P.status + HFE_STATUS_LIST_LEN, 1u);
-                if (at < (unsigned)HFE_WORKLIST_CAPACITY) P.status[HFE_STATUS_HEADER_WORDS + at] = (unsigned)row;
-                else atomicOr(P.status, HFE_WORKLIST_OVERFLOW);
-            }
-            if (nonfinite && valid) atomicOr(P.status, HFE_ROW_NONFINITE);
-            if (P.y && P.score) {                                       // accuracy count; flagged rows are counted by the fix-up
-                unsigned hits = (valid && !fix && lab == P.y[row]) ? 1u : 0u;
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1) hits += __shfl_down_sync(0xFFFFFFFFu, hits, o);
-                if (lane == 0 && hits) atomicAdd(P.score, (unsigned long long)hits);
-            }
+            // hand the row's sum to the producer thread that finishes it
+            ring_sum((int)(i % MMA_RING))[row_in_tile] = widen_f32(acc_hi) + widen_f32(acc_lo);
+            ring_lin((int)(i % MMA_RING))[row_in_tile] = __uint_as_float(lin_dot);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar(B_SUMFULL + (int)(i % MMA_RING)));
         }
     } else {
         // =========================== MMA issuers: one lane per stream =============================================================
-        const int s = warp - (MMA_PRODUCER_WARPS + MMA_EPI_WARPS);
+        const int s = warp - MMA_ISSUE_WARP0;
         if (lane == 0) {
             mbar_wait(bar(B_W), 0);
-            // instruction descriptor (cute::UMMA::InstrDescriptor): D float32, A and B bfloat16, both K-major, N = 64, M = 128
-            const unsigned idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((unsigned)(MMA_BLOCK_SV >> 3) << 17) | ((128u >> 4) << 24);
+            // instruction descriptor (cute::UMMA::InstrDescriptor): D float32, A and B bfloat16, both K-major, N = bsv, M = 128
+            const unsigned idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((unsigned)(bsv >> 3) << 17) | ((128u >> 4) << 24);
             const unsigned a_sbo = MMA_A_CHUNKS * 128, b_sbo = MMA_B_CHUNKS * 128;
             long long j = 0;
             for (long long i = s, tile = blockIdx.x + (long long)s * gridDim.x; tile < n_tiles; i += 2, tile += 2LL * gridDim.x, ++j) {
@@ -410,25 +468,25 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
                     const int reg = (int)(use & 1);
                     mbar_wait(bar(B_ACCEMPTY + 2 * s + reg), (unsigned)(((use >> 1) & 1) ^ 1));
                     tc_fence_after();
-                    const unsigned d_hi = tmem_base + (unsigned)((2 * s + reg) * (2 * MMA_BLOCK_SV)), d_rest = d_hi + MMA_BLOCK_SV;
-                    const unsigned b_base = smem_addr(s_w) + (unsigned)(blk * (MMA_BLOCK_SV / 8)) * b_sbo;
+                    const unsigned d = tmem_base + (unsigned)((2 * s + reg) * MMA_REGION_COLS);
+                    const unsigned b_base = smem_addr(s_w) + (unsigned)(blk * (bsv / 8)) * b_sbo;
                     auto a_desc = [&](int ks) { return umma_desc(a_base + ks * 256, 128, a_sbo); };
                     auto b_desc = [&](int chunk, int lbo_chunks) { return umma_desc(b_base + chunk * 128, lbo_chunks * 128, b_sbo); };
-                    // A chunks  H0 H1 H2 0 | H0 H1 H2 H0 H1 H2        B chunks  WH0 WH1 WH2 0 | WM0 WM1 WM2 WL0 WL1 WL2
-                    umma_bf16(d_hi, a_desc(0), b_desc(0, 1), idesc, 0u);          // (H0 H1).(WH0 WH1)
-                    umma_bf16(d_hi, a_desc(1), b_desc(2, 1), idesc, 1u);          // (H2 0).(WH2 0)
-                    umma_bf16(d_rest, a_desc(2), b_desc(4, 1), idesc, 0u);        // (H0 H1).(WM0 WM1)
-                    umma_bf16(d_rest, a_desc(3), b_desc(6, 1), idesc, 1u);        // (H2 H0).(WM2 WL0)
-                    umma_bf16(d_rest, a_desc(4), b_desc(8, 1), idesc, 1u);        // (H1 H2).(WL1 WL2)
+                    // B chunks  WL0 WL1 WL2 WM0 WM1 WM2 WH0 WH1 WH2 0.  Smallest products first.
                     if (ext) {
-                        // extension chunks  M0 M1 M2 M0 M1 M2 L0 L1 L2 0  (mid and lo parts of the centred features): all of it
-                        // is 2^-8 and below, so it joins the rest accumulator
-                        umma_bf16(d_rest, a_desc(5), b_desc(0, 1), idesc, 1u);    // (M0 M1).(WH0 WH1)
-                        umma_bf16(d_rest, a_desc(6), b_desc(2, 2), idesc, 1u);    // (M2 M0).(WH2 WM0)
-                        umma_bf16(d_rest, a_desc(7), b_desc(5, 1), idesc, 1u);    // (M1 M2).(WM1 WM2)
-                        umma_bf16(d_rest, a_desc(8), b_desc(0, 1), idesc, 1u);    // (L0 L1).(WH0 WH1)
-                        umma_bf16(d_rest, a_desc(9), b_desc(2, 1), idesc, 1u);    // (L2 0).(WH2 0)
+                        // A extension chunks  L0 L1 | M0 L2 | M1 M2 | M0 M1 | M2 0
+                        umma_bf16(d, a_desc(5), b_desc(6, 1), idesc, 0u);         // (L0 L1).(WH0 WH1)        2^-16
+                        umma_bf16(d, a_desc(6), b_desc(3, 5), idesc, 1u);         // (M0 L2).(WM0 WH2)        2^-16
+                        umma_bf16(d, a_desc(7), b_desc(4, 1), idesc, 1u);         // (M1 M2).(WM1 WM2)        2^-16
+                        umma_bf16(d, a_desc(8), b_desc(6, 1), idesc, 1u);         // (M0 M1).(WH0 WH1)        2^-8
+                        umma_bf16(d, a_desc(9), b_desc(8, 1), idesc, 1u);         // (M2 0).(WH2 0)           2^-8
                     }
+                    // A base chunks  H0 H1 | H2 H0 | H1 H2 | H0 H1 | H2 0
+                    umma_bf16(d, a_desc(0), b_desc(0, 1), idesc, ext ? 1u : 0u);  // (H0 H1).(WL0 WL1)        2^-16
+                    umma_bf16(d, a_desc(1), b_desc(2, 1), idesc, 1u);             // (H2 H0).(WL2 WM0)
+                    umma_bf16(d, a_desc(2), b_desc(4, 1), idesc, 1u);             // (H1 H2).(WM1 WM2)        2^-8
+                    umma_bf16(d, a_desc(3), b_desc(6, 1), idesc, 1u);             // (H0 H1).(WH0 WH1)        1
+                    umma_bf16(d, a_desc(4), b_desc(8, 1), idesc, 1u);             // (H2 0).(WH2 0)
                     tc_commit(bar(B_ACCFULL + 2 * s + reg));
                 }
                 tc_commit(bar(B_AEMPTY + stage));
@@ -437,7 +495,7 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 12) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512));
+    if (warp == MMA_ISSUE_WARP0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512));
 }
 
 }  // namespace hfe

@@ -125,18 +125,21 @@ struct ScoreParams {
 };
 
 // Tensor-core path of the RBF sum (hfe_mma.cuh): the B operand image and what the producers need to build the A operand.
-constexpr int MMA_BLOCK_SV = 64;      // support vectors per TMEM region (N of one MMA instruction)
-constexpr int MMA_MAX_SV = 512;       // 8 blocks x [hi | rest] accumulators = the 512 TMEM columns, 4 regions in flight
-constexpr int MMA_B_CHUNKS = 10;      // 16-byte K chunks per support vector: WH0 WH1 WH2 0 | WM0 WM1 WM2 WL0 WL1 WL2
+constexpr int MMA_MAX_SV = 512;       // 4 blocks of up to 128 support vectors = the 512 TMEM columns (4 regions in flight)
+constexpr int MMA_B_CHUNKS = 10;      // 16-byte K chunks per support vector: WL0 WL1 WL2 WM0 WM1 WM2 WH0 WH1 WH2 0
 
 struct MmaParams {
-    const unsigned char* w_img;     // [n_pad/8][MMA_B_CHUNKS][8][16 B] bfloat16 B operand, then float coef[n_pad]
+    const unsigned char* w_img;     // [n_pad/8][MMA_B_CHUNKS][8][16 B] bfloat16 B operand, then float coef'[n_pad]
     int w_bytes;                    // image + coefficient table
-    int nb;                         // blocks of MMA_BLOCK_SV support vectors; n_pad = 64 * nb; 0 = path not available
+    int nb;                         // blocks of block_sv support vectors; n_pad = nb * block_sv; 0 = path not available
+    int block_sv;                   // multiple of 16, at most 128 (N of one MMA instruction = columns of one TMEM region)
+    int pad_;
     float center[F];                // m_d: the scaler mean rounded to an integer
-    double dmean[F];                // m_d - mean_d
-    double inv_var[F];              // 1 / scale_d^2
-    double neg_c;                   // -gamma * log2(e)
+    float zz_a[F], zz_b[F];         // |z|^2 = sum_d xc_d (a_d xc_d + b_d) + c,  xc = x - m
+    float zz_c;
+    float wmax_all;                 // max_dj |W_dj| (slightly enlarged): |exponent of a row| <= wmax_all * sum_d |xc_d|
+    double lin_base;                // logistic member: intercept + sum_d m_d * coef_d; the dot product over x - m is the last
+                                    // column of the B operand (coefficient 0 in the RBF sum) and comes off the tensor core
 };
 
 struct HostPipeline;            // hfe_host.cuh: pinned / device slots and the thread pool of large host calls
@@ -153,6 +156,7 @@ struct Model {
     double gbt_guard = 0.0;       // assumed |error| of the float32 boosted raw score
     ScoreParams base{};           // request fields zero; table pointers filled
     MmaParams mma{};              // nb > 0: the RBF sum can run on the tensor cores
+    std::vector<unsigned char> mma_img_host;   // B operand image while the model is being built (uploaded by build_model)
     int rbf_engine = 0;           // 0 = automatic (tensor cores when available), 1 = SIMT FFMA2 loop, 2 = tensor cores
     std::vector<void*> allocations;
     uint64_t device_bytes = 0;
@@ -506,11 +510,11 @@ inline int build_svc(Model* m, const ParsedBlob& pb, uint32_t idx) {
         }
     }
     // ---- tensor-core operand image (hfe_mma.cuh) -------------------------------------------------------------------------
-    // t_j = sum_d xc_d W_dj + B_j + r, every number carried as three bfloat16 parts.  Column j of the image is support
-    // vector order[j] (signs alternating, so the float32 partial sums of the epilogue stay small); pad columns have zero
-    // weights and a zero coefficient.
+    // T_j = sum_d xc_d W_dj with W_dj carried as three bfloat16 parts; coef'_j = coef_j 2^(B_j).  Column j of the image is
+    // support vector order[j] (signs alternating, so the float32 partial sums of the epilogue stay small); pad columns have
+    // zero weights and a zero coefficient.
     std::vector<unsigned char> mma_img;
-    if (n_sv <= MMA_MAX_SV) {
+    if (n_sv < MMA_MAX_SV) {
         MmaParams& Q = m->mma;
         auto bf16_bits = [](float v) -> uint16_t {              // round to nearest even, like cvt.rn.bf16.f32
             uint32_t b;
@@ -519,60 +523,56 @@ inline int build_svc(Model* m, const ParsedBlob& pb, uint32_t idx) {
             return (uint16_t)(b >> 16);
         };
         auto bf16_val = [](uint16_t h) { uint32_t b = (uint32_t)h << 16; float v; std::memcpy(&v, &b, 4); return v; };
-        auto split3 = [&](double v, uint16_t out[3]) {
-            double rest = v;
-            for (int k = 0; k < 3; ++k) {
-                out[k] = bf16_bits((float)rest);
-                rest -= (double)bf16_val(out[k]);
-            }
-        };
-        const int nb = (n_sv + MMA_BLOCK_SV - 1) / MMA_BLOCK_SV, n_pad = nb * MMA_BLOCK_SV;
+        const int n_cols = n_sv + 1;                        // the last column carries the logistic member's dot product
+        const int nb = (n_cols + 127) / 128, per_block = (n_cols + nb - 1) / nb;
+        const int bsv = ((per_block + 15) / 16) * 16, n_pad = nb * bsv;
         const size_t img_bytes = (size_t)n_pad * MMA_B_CHUNKS * 16;
         mma_img.assign(img_bytes + (size_t)n_pad * sizeof(float), 0);
         float* coef_tab = reinterpret_cast<float*>(mma_img.data() + img_bytes);
+        double zz_c = 0.0;
         for (int d = 0; d < F; ++d) {
             Q.center[d] = (float)std::nearbyint(P.mean[d]);
-            Q.dmean[d] = (double)Q.center[d] - P.mean[d];
-            Q.inv_var[d] = 1.0 / (P.scale[d] * P.scale[d]);
+            const double dm = (double)Q.center[d] - P.mean[d], iv = 1.0 / (P.scale[d] * P.scale[d]);
+            Q.zz_a[d] = (float)iv;
+            Q.zz_b[d] = (float)(2.0 * dm * iv);
+            zz_c += dm * dm * iv;
         }
-        Q.neg_c = -P.c_log2;
-        const uint16_t one = bf16_bits(1.f);
+        Q.zz_c = (float)zz_c;
+        Q.wmax_all = 0.f;
+        bool usable = true;
         for (int col = 0; col < n_sv; ++col) {
             const int j = order[col];
             const double* s = sv->f64() + (size_t)j * F;
             uint16_t* row = reinterpret_cast<uint16_t*>(mma_img.data() + (size_t)(col / 8) * (MMA_B_CHUNKS * 128) + (col % 8) * 16);
-            auto at = [&](int chunk, int e) -> uint16_t& { return row[chunk * 64 + e]; };     // chunks are 128 bytes apart
             double bias = 0.0, ss = 0.0;
             for (int d = 0; d < F; ++d) {
                 const double w = 2.0 * P.c_log2 * s[d] / P.scale[d];
-                uint16_t p[3];
-                split3(w, p);
-                // feature d sits in chunk d / 8 of its part, element d % 8; parts: hi chunks 0-2, mid 4-6, lo 7-9
-                at(0 + d / 8, d % 8) = p[0];
-                at(4 + d / 8, d % 8) = p[1];
-                at(7 + d / 8, d % 8) = p[2];
-                bias += Q.dmean[d] * w;
+                double rest = w;
+                for (int part = 0; part < 3; ++part) {           // hi, mid, lo; chunks are 128 bytes (64 elements) apart
+                    const uint16_t h = bf16_bits((float)rest);
+                    rest -= (double)bf16_val(h);
+                    row[(6 - 3 * part + d / 8) * 64 + d % 8] = h;       // lo parts in chunks 0-2, mid 3-5, hi 6-8
+                }
+                Q.wmax_all = std::max(Q.wmax_all, (float)(std::fabs(w) * 1.01));
+                bias += ((double)Q.center[d] - P.mean[d]) * w;
                 ss += s[d] * s[d];
             }
             bias -= P.c_log2 * ss;
-            uint16_t bp[3];
-            split3(bias, bp);
-            // slot 1 of the third chunk multiplies the constant 1 of the A operand (bias); slots 2-4 select the three parts
-            // of the row term r: its hi part goes to the hi accumulator, mid and lo to the rest accumulator
-            at(2, 1) = bp[0]; at(6, 1) = bp[1]; at(9, 1) = bp[2];
-            at(2, 2) = one;   at(6, 3) = one;   at(6, 4) = one;
-            coef_tab[col] = (float)coef[j];
+            const double folded = coef[j] * std::exp2(bias);
+            usable = usable && std::isfinite(folded) && std::fabs(bias) <= 100.0;
+            coef_tab[col] = (float)folded;
         }
-        for (int col = n_sv; col < n_pad; ++col) {                   // pad columns still need the row term (exponent <= 0)
-            uint16_t* row = reinterpret_cast<uint16_t*>(mma_img.data() + (size_t)(col / 8) * (MMA_B_CHUNKS * 128) + (col % 8) * 16);
-            row[2 * 64 + 2] = one; row[6 * 64 + 3] = one; row[6 * 64 + 4] = one;
+        if (usable) {
+            Q.nb = nb;
+            Q.block_sv = bsv;
+            Q.w_bytes = (int)mma_img.size();
+        } else {
+            mma_img.clear();
         }
-        Q.nb = nb;
-        Q.w_bytes = (int)mma_img.size();
     }
     std::vector<double> sv_host(sv->f64(), sv->f64() + (size_t)n_sv * F), dual_host(coef, coef + n_sv);
     int rc;
-    if (!mma_img.empty() && (rc = upload(m, mma_img, &m->mma.w_img))) return rc;
+    m->mma_img_host.swap(mma_img);          // the logistic member's column is added once that member has been read
     if ((rc = upload(m, tab, &P.sv_tab))) return rc;
     if ((rc = upload(m, sv_host, &P.sv64))) return rc;
     if ((rc = upload(m, dual_host, &P.dual64))) return rc;
@@ -865,6 +865,33 @@ inline int build_model(const uint8_t* blob, size_t len, int device, Model** out)
         }
     }
     if (rc == HFE_OK) {
+        if (m->mma.nb > 0 && !m->mma_img_host.empty()) {
+            // logistic member on the tensor core: its coefficients (three bfloat16 parts each, like the W columns) are the
+            // last column of the B operand; that column's RBF coefficient is zero
+            MmaParams& Q = m->mma;
+            Q.lin_base = P.lin_intercept;
+            const int col = Q.nb * Q.block_sv - 1;
+            uint16_t* row = reinterpret_cast<uint16_t*>(m->mma_img_host.data() + (size_t)(col / 8) * (MMA_B_CHUNKS * 128) + (col % 8) * 16);
+            for (int d = 0; d < F; ++d) {
+                Q.lin_base += (double)Q.center[d] * P.lin_coef[d];
+                double rest = P.slot_lin >= 0 ? P.lin_coef[d] : 0.0;
+                for (int part = 0; part < 3; ++part) {
+                    float v = (float)rest;
+                    uint32_t b;
+                    std::memcpy(&b, &v, 4);
+                    b += 0x7FFFu + ((b >> 16) & 1u);
+                    const uint16_t h = (uint16_t)(b >> 16);
+                    const uint32_t hb = (uint32_t)h << 16;
+                    float hv;
+                    std::memcpy(&hv, &hb, 4);
+                    rest -= (double)hv;
+                    row[(6 - 3 * part + d / 8) * 64 + d % 8] = h;
+                }
+            }
+            rc = upload(m, m->mma_img_host, &Q.w_img);
+            m->mma_img_host.clear();
+            m->mma_img_host.shrink_to_fit();
+        }
         P.final_intercept = fin->f64()[pb.n_members];
         // guard bands: how far the float32 decision value may be off, pushed through the Platt slope
         double slope = std::fabs(P.prob_a) * 0.25;                       // |d r / d f| <= |A|/4
