@@ -144,7 +144,7 @@ template <int TM>
 int launch_mma(const Model* m, const ScoreParams& P, cudaStream_t stream) {
     const MmaParams& Q = m->mma;
     const size_t smem = (((size_t)Q.w_bytes + 1023) & ~(size_t)1023) + (size_t)MMA_A_STAGES * MMA_A_STAGE_BYTES +
-                        (size_t)MMA_RING * MMA_RING_SLOT_BYTES + 32 * sizeof(unsigned long long) + 64;
+                        (size_t)MMA_RING * MMA_RING_SLOT_BYTES + 48 * sizeof(unsigned long long) + 128;
     auto kernel = hfe_mma_kernel<TM>;
     static std::mutex mu;
     static std::map<int, int> ready;
@@ -335,6 +335,14 @@ int hfe_model_get_info(const hfe_model* model, hfe_model_info* info) {
     fill_info(model->impl, info);
     return HFE_OK;
 }
+
+#ifdef HFE_MMA_TRACE
+int hfe_debug_trace(unsigned long long* out32, int reset) {
+    if (out32) HFE_CUDA_TRY(cudaMemcpyFromSymbol(out32, g_mma_trace, sizeof(unsigned long long) * 32));
+    if (reset) { unsigned long long z[32] = {}; HFE_CUDA_TRY(cudaMemcpyToSymbol(g_mma_trace, z, sizeof(z))); }
+    return HFE_OK;
+}
+#endif
 
 int hfe_model_set_rbf_engine(hfe_model* model, int engine) {
     if (!model || !model->impl) return fail(HFE_ERR_INVALID_ARGUMENT, "null model handle");

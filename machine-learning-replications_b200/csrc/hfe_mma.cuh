@@ -9,8 +9,8 @@
 // The operands are bfloat16 but nothing is rounded away: every W_dj is split into three bfloat16 parts (hi + mid + lo =
 // 24 significant bits) and so is xc_d; products of 8-bit significands are exact in the float32 accumulator.  For
 // cohorts in the load_data_public.py schema every feature is a small integer, xc_d is one exact bfloat16 and the base
-// block (5 K-steps of 16) is all there is; when a tile holds a value that needs more bits the issuing thread puts the
-// extension block (mid and lo parts of xc, 5 more K-steps) in front of it for that tile only.
+// block (6 K-steps of 16) is all there is; when a tile holds a value that needs more bits the issuing thread puts the
+// extension block (mid and lo parts of xc, 6 more K-steps) in front of it for that tile only.
 // The tensor core aligns the products of one instruction and the accumulator to the largest exponent among them and
 // drops what falls below ~2^-24 of it (measured with tools/mma_probe.cu).  Hence: the large constant terms (B_j, the
 // row term) stay out of the accumulator, and K-steps run from the smallest parts to the largest, so each accumulation
@@ -24,7 +24,8 @@
 //               combiner (finish_rows_fast), four tiles at a time so that four float64 chains are interleaved
 //   warps 4-7   exponent warps of stream 0, warps 8-11 of stream 1: thread = row (TMEM lane); tcgen05.ld 16 columns at a
 //               time, ex2, coefficient FFMA2, float64 fold -- nothing else, so that the MUFU pipe always has work
-//   warps 12,13 one lane each issues the tcgen05.mma instructions of its stream and commits them to mbarriers
+//               lane 0 of the first warp of each stream also issues the stream's tcgen05.mma instructions: as soon as the
+//               four warps have drained a region it refills it with the block two ahead and commits to an mbarrier
 // Tiles alternate between the two streams.  Support vectors are taken in blocks of up to 128; TMEM (512 columns) is cut
 // into four regions, two per stream: while a stream's epilogue warps drain one block from one region the tensor core
 // fills the other, and the other stream keeps the MUFU pipe busy in the meantime.  Both the MUFU pipe and the TMEM read
@@ -38,14 +39,13 @@
 namespace hfe {
 
 constexpr int MMA_TILE_ROWS = 128;
-constexpr int MMA_PRODUCER_WARPS = 4, MMA_FINISH_WARPS = 2, MMA_EPI_WARPS = 8, MMA_ISSUE_WARPS = 2;
-constexpr int MMA_EPI_WARP0 = MMA_PRODUCER_WARPS + MMA_FINISH_WARPS;             // 6: exponent warps 6..13
-constexpr int MMA_ISSUE_WARP0 = MMA_EPI_WARP0 + MMA_EPI_WARPS;                   // 14, 15
-constexpr int MMA_THREADS = 32 * (MMA_PRODUCER_WARPS + MMA_FINISH_WARPS + MMA_EPI_WARPS + MMA_ISSUE_WARPS);   // 512
-constexpr int MMA_A_STAGES = 3;
-constexpr int MMA_A_CHUNKS = 20;                         // 16-byte K chunks per row: 10 base + 10 extension
-constexpr int MMA_A_STAGE_BYTES = (MMA_TILE_ROWS / 8) * MMA_A_CHUNKS * 128;                   // 40 960
-constexpr int MMA_RING = 8;                              // tiles between a row's production and its float64 epilogue
+constexpr int MMA_PRODUCER_WARPS = 4, MMA_FINISH_WARPS = 4, MMA_EPI_WARPS = 8;
+constexpr int MMA_EPI_WARP0 = MMA_PRODUCER_WARPS + MMA_FINISH_WARPS;             // exponent warps 8..15
+constexpr int MMA_THREADS = 32 * (MMA_PRODUCER_WARPS + MMA_FINISH_WARPS + MMA_EPI_WARPS);   // 512
+constexpr int MMA_A_STAGES = 5;                          // two tiles in the tensor core / exponent warps, three produced ahead
+constexpr int MMA_A_CHUNKS = 12;                         // 16-byte K chunks per row: H0 H1 H2 0 | M0 M1 M2 0 | L0 L1 L2 0
+constexpr int MMA_A_STAGE_BYTES = (MMA_TILE_ROWS / 8) * MMA_A_CHUNKS * 128;                   // 24 576
+constexpr int MMA_RING = 12;                             // tiles between a row's production and its float64 epilogue
 constexpr int MMA_RING_SLOT_BYTES = MMA_TILE_ROWS * 20;  // per tile and row: RBF sum (f64), logistic dot, stump score, gamma|z|^2 (f32)
 constexpr int MMA_REGION_COLS = 128;                     // TMEM columns per region
 constexpr int MMA_TAIL_ROWS = 4;                         // tiles whose float64 epilogue one thread runs interleaved
@@ -133,6 +133,14 @@ __device__ __forceinline__ void two_sum_add(float& hi, float& lo, float v) {
     hi = s;
 }
 
+#ifdef HFE_MMA_TRACE
+// development builds: where the warps wait (clock cycles summed over lane 0 of the waiting warps)
+__device__ unsigned long long g_mma_trace[32];
+#define MMA_TRACE_WAIT(slot, stmt) do { const long long t0_ = clock64(); stmt; if (lane == 0) atomicAdd(&g_mma_trace[slot], (unsigned long long)(clock64() - t0_)); } while (0)
+#else
+#define MMA_TRACE_WAIT(slot, stmt) do { stmt; } while (0)
+#endif
+
 // ---- the kernel ------------------------------------------------------------------------------------------------------------
 template <int TREE_MODE>
 __global__ void __launch_bounds__(MMA_THREADS, 1)
@@ -145,8 +153,10 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
     unsigned char* s_a = smem + w_region;
     unsigned char* s_ring = s_a + MMA_A_STAGES * MMA_A_STAGE_BYTES;
     unsigned long long* s_bar = reinterpret_cast<unsigned long long*>(s_ring + MMA_RING * MMA_RING_SLOT_BYTES);
-    unsigned* s_misc = reinterpret_cast<unsigned*>(s_bar + 32);
-    enum { B_W = 0, B_AFULL = 1, B_AEMPTY = 4, B_ACCFULL = 7, B_ACCEMPTY = 11, B_SUMFULL = 15, B_RINGFREE = 23 };
+    unsigned* s_misc = reinterpret_cast<unsigned*>(s_bar + 48);
+    enum { B_W = 0, B_AFULL = 1, B_AEMPTY = B_AFULL + MMA_A_STAGES, B_ACCFULL = B_AEMPTY + MMA_A_STAGES, B_ACCEMPTY = B_ACCFULL + 4,
+           B_SUMFULL = B_ACCEMPTY + 4, B_RINGFREE = B_SUMFULL + MMA_RING, B_COUNT = B_RINGFREE + MMA_RING };
+    static_assert(B_COUNT <= 48, "barrier block");
     auto bar = [&](int i) { return smem_addr(s_bar + i); };
     auto ring_sum = [&](int slot) { return reinterpret_cast<double*>(s_ring + slot * MMA_RING_SLOT_BYTES); };
     auto ring_lin = [&](int slot) { return reinterpret_cast<float*>(s_ring + slot * MMA_RING_SLOT_BYTES + MMA_TILE_ROWS * 8); };
@@ -171,7 +181,7 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
         for (int i = 0; i < MMA_RING; ++i) { mbar_init(bar(B_SUMFULL + i), 4); mbar_init(bar(B_RINGFREE + i), MMA_FINISH_WARPS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == MMA_ISSUE_WARP0) {
+    if (warp == MMA_EPI_WARP0) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_addr((const void*)s_tmem)), "r"(512));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
     }
@@ -262,25 +272,18 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
             }
             if (nonfinite) atomicOr(P.status, HFE_ROW_NONFINITE);
             // what the finishing warps need besides the RBF sum (they have released slot i % 8 of the ring after tile i - 8)
-            mbar_wait(bar(B_RINGFREE + (int)(i % MMA_RING)), (unsigned)(((i / MMA_RING) & 1) ^ 1));
+            MMA_TRACE_WAIT(12, mbar_wait(bar(B_RINGFREE + (int)(i % MMA_RING)), (unsigned)(((i / MMA_RING) & 1) ^ 1)));
             ring_raw((int)(i % MMA_RING))[prow] = raw32;
             ring_gzz((int)(i % MMA_RING))[prow] = fix_row ? -1.f : (float)P.gamma * zz;
 
-            mbar_wait(bar(B_AEMPTY + stage), (unsigned)(((i / MMA_A_STAGES) & 1) ^ 1));
-            // A operand: [row group][chunk][row in group][8 bf16]; base chunks H0 H1 H2 H0 H1 H2 H0 H1 H2 0 meet the lo, mid and
-            // hi parts of W in that order (chunk 9 stays zero)
+            MMA_TRACE_WAIT(11, mbar_wait(bar(B_AEMPTY + stage), (unsigned)(((i / MMA_A_STAGES) & 1) ^ 1)));
+            // A operand: [row group][chunk][row in group][8 bf16], chunks H0 H1 H2 0 | M0 M1 M2 0 | L0 L1 L2 0 (hi, mid, lo parts
+            // of the centred features; the zero chunks are never written).  Only tiles holding a value that one bfloat16
+            // cannot carry use the mid / lo chunks, but then the rows of all four warps must be there.
             unsigned char* a_row = s_a + stage * MMA_A_STAGE_BYTES + (prow >> 3) * (MMA_A_CHUNKS * 128) + (prow & 7) * 16;
-            const uint4 h0 = make_uint4(hp[0], hp[1], hp[2], hp[3]);
-            const uint4 h1 = make_uint4(hp[4], hp[5], hp[6], hp[7]);
-            const uint4 h2 = make_uint4(hp[8], 0u, 0u, 0u);
-#pragma unroll
-            for (int rep = 0; rep < 3; ++rep) {
-                *reinterpret_cast<uint4*>(a_row + (3 * rep + 0) * 128) = h0;
-                *reinterpret_cast<uint4*>(a_row + (3 * rep + 1) * 128) = h1;
-                *reinterpret_cast<uint4*>(a_row + (3 * rep + 2) * 128) = h2;
-            }
-            // extension chunks L0 L1 M0 L2 M1 M2 M0 M1 M2 0 (mid and lo parts of the centred features): only tiles holding a value
-            // that one bfloat16 cannot carry use them, but then the rows of all four warps must be there
+            *reinterpret_cast<uint4*>(a_row + 0 * 128) = make_uint4(hp[0], hp[1], hp[2], hp[3]);
+            *reinterpret_cast<uint4*>(a_row + 1 * 128) = make_uint4(hp[4], hp[5], hp[6], hp[7]);
+            *reinterpret_cast<uint4*>(a_row + 2 * 128) = make_uint4(hp[8], 0u, 0u, 0u);
             const bool ext = __any_sync(0xFFFFFFFFu, inexact);
             if (!keep) {
 #pragma unroll
@@ -288,22 +291,25 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
             }
             uint4 m0 = make_uint4(0, 0, 0, 0), m1 = m0, m2 = m0, l0 = m0, l1 = m0, l2 = m0;
             if (ext) {
-                float mid[F], lo[F];
+                unsigned mp[9];
+                float lo[F];
 #pragma unroll
-                for (int f = 0; f < F; ++f) { mid[f] = bf16_round(rem[f]); lo[f] = bf16_round(rem[f] - mid[f]); }
-                m0 = make_uint4(pack_bf16(mid[0], mid[1]), pack_bf16(mid[2], mid[3]), pack_bf16(mid[4], mid[5]), pack_bf16(mid[6], mid[7]));
-                m1 = make_uint4(pack_bf16(mid[8], mid[9]), pack_bf16(mid[10], mid[11]), pack_bf16(mid[12], mid[13]), pack_bf16(mid[14], mid[15]));
-                m2 = make_uint4(pack_bf16(mid[16], 0.f), 0u, 0u, 0u);
+                for (int k = 0; k < 8; ++k) mp[k] = pack_bf16(rem[2 * k], rem[2 * k + 1]);
+                mp[8] = pack_bf16(rem[16], 0.f);
+#pragma unroll
+                for (int f = 0; f < F; ++f)
+                    lo[f] = rem[f] - __uint_as_float((f & 1) ? (mp[f >> 1] & 0xFFFF0000u) : (mp[f >> 1] << 16));
+                m0 = make_uint4(mp[0], mp[1], mp[2], mp[3]);
+                m1 = make_uint4(mp[4], mp[5], mp[6], mp[7]);
+                m2 = make_uint4(mp[8], 0u, 0u, 0u);
                 l0 = make_uint4(pack_bf16(lo[0], lo[1]), pack_bf16(lo[2], lo[3]), pack_bf16(lo[4], lo[5]), pack_bf16(lo[6], lo[7]));
                 l1 = make_uint4(pack_bf16(lo[8], lo[9]), pack_bf16(lo[10], lo[11]), pack_bf16(lo[12], lo[13]), pack_bf16(lo[14], lo[15]));
                 l2 = make_uint4(pack_bf16(lo[16], 0.f), 0u, 0u, 0u);
             }
-            unsigned char* e_row = a_row + 10 * 128;
-            *reinterpret_cast<uint4*>(e_row + 0 * 128) = l0; *reinterpret_cast<uint4*>(e_row + 1 * 128) = l1;
-            *reinterpret_cast<uint4*>(e_row + 2 * 128) = m0; *reinterpret_cast<uint4*>(e_row + 3 * 128) = l2;
-            *reinterpret_cast<uint4*>(e_row + 4 * 128) = m1; *reinterpret_cast<uint4*>(e_row + 5 * 128) = m2;
-            *reinterpret_cast<uint4*>(e_row + 6 * 128) = m0; *reinterpret_cast<uint4*>(e_row + 7 * 128) = m1;
-            *reinterpret_cast<uint4*>(e_row + 8 * 128) = m2;
+            *reinterpret_cast<uint4*>(a_row + 4 * 128) = m0; *reinterpret_cast<uint4*>(a_row + 5 * 128) = m1;
+            *reinterpret_cast<uint4*>(a_row + 6 * 128) = m2;
+            *reinterpret_cast<uint4*>(a_row + 8 * 128) = l0; *reinterpret_cast<uint4*>(a_row + 9 * 128) = l1;
+            *reinterpret_cast<uint4*>(a_row + 10 * 128) = l2;
             if (lane == 0) s_ext[stage * 4 + warp] = ext ? 1u : 0u;
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");           // these stores before the tensor core's reads
             __syncwarp();
@@ -315,29 +321,28 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
             mbar_wait(bar(B_AEMPTY + (int)(k % MMA_A_STAGES)), (unsigned)((k / MMA_A_STAGES) & 1));
     } else if (warp < MMA_EPI_WARP0) {
         // =========================== finishing warps: the float64 epilogue of every row ===========================================
-        // 64 threads; thread t finishes rows t and t + 64 of two consecutive tiles at a time, so four independent float64
-        // chains (Platt, clamp, coupling, links, combiner: the SIMT kernel's epilogue code) are interleaved
+        // thread = row; the rows of four consecutive tiles are finished together, so four independent float64 chains
+        // (Platt, clamp, coupling, links, combiner: the SIMT kernel's epilogue code) are interleaved
         constexpr int R = MMA_TAIL_ROWS;
         const bool has_lin = P.slot_lin >= 0;
-        const int frow = tid - 32 * MMA_PRODUCER_WARPS;        // 0..63
+        const int prow = tid - 32 * MMA_PRODUCER_WARPS;        // 0..127
         const long long my_tiles = (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x;
-        for (long long t0 = 0; t0 < my_tiles; t0 += 2) {
-            const int count = my_tiles - t0 >= 2 ? 2 : 1;
+        for (long long t0 = 0; t0 < my_tiles; t0 += R) {
+            const int count = (int)(my_tiles - t0 >= R ? R : my_tiles - t0);
             double f_svc[R], zpart[R], p1[R], zfin[R], p_svc[R], raw[R], zl[R], member[3][R];
             float gzz[R];
             long long rows[R];
             bool unc[R];
 #pragma unroll
             for (int r = 0; r < R; ++r) {
-                const long long t = t0 + (r >> 1);
-                const int prow = frow + 64 * (r & 1);
+                const long long t = t0 + r;
                 rows[r] = P.n;
                 f_svc[r] = P.svc_intercept;
                 raw[r] = zl[r] = 0.0;
                 gzz[r] = 0.f;
-                if ((r >> 1) < count) {
+                if (r < count) {
                     const int slot = (int)(t % MMA_RING);
-                    mbar_wait(bar(B_SUMFULL + slot), (unsigned)((t / MMA_RING) & 1));
+                    MMA_TRACE_WAIT(13, mbar_wait(bar(B_SUMFULL + slot), (unsigned)((t / MMA_RING) & 1)));
                     rows[r] = ((long long)blockIdx.x + t * gridDim.x) * MMA_TILE_ROWS + prow;
                     gzz[r] = ring_gzz(slot)[prow];
                     raw[r] = P.gbt_split_base + (double)ring_raw(slot)[prow];
@@ -347,8 +352,9 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
             }
             __syncwarp();
             if (lane == 0) {                                    // the ring slots may be rewritten
-                mbar_arrive(bar(B_RINGFREE + (int)(t0 % MMA_RING)));
-                if (count == 2) mbar_arrive(bar(B_RINGFREE + (int)((t0 + 1) % MMA_RING)));
+#pragma unroll
+                for (int r = 0; r < R; ++r)
+                    if (r < count) mbar_arrive(bar(B_RINGFREE + (int)((t0 + r) % MMA_RING)));
             }
             partial_logit_fast<R>(P, TREE_MODE != 0, has_lin, raw, zl, zpart, member);
             finish_rows_fast<R>(P, true, f_svc, zpart, p1, zfin, p_svc, unc);
@@ -383,7 +389,7 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
                 if (lane == 0 && hits) atomicAdd(P.score, (unsigned long long)hits);
             }
         }
-    } else if (warp < MMA_ISSUE_WARP0) {
+    } else {
         // =========================== exponent warps ================================================================================
         const int s = (warp - MMA_EPI_WARP0) >> 2;                   // stream
         const int row_in_tile = (warp & 3) * 32 + lane;              // TMEM lane = row of the tile (warp % 4 picks the lane quarter)
@@ -391,6 +397,67 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
         mbar_wait(bar(B_W), 0);
         const float* s_coef = reinterpret_cast<const float*>(s_w + (size_t)nb * bsv * (MMA_B_CHUNKS * 16));
         const int steps = bsv >> 4;
+        // ---- MMA issue: lane 0 of the stream's first warp.  Blocks of the stream's tiles are issued in order, each into the
+        //      region the four warps have just drained (the first two go into the still empty regions). ----------------------
+        const bool issuer = ((warp & 3) == 0) && lane == 0;
+        // instruction descriptor (cute::UMMA::InstrDescriptor): D float32, A and B bfloat16, both K-major, N = bsv, M = 128
+        const unsigned idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((unsigned)(bsv >> 3) << 17) | ((128u >> 4) << 24);
+        // descriptors are built once; per instruction only the 14-bit start-address field (16-byte units, low word) moves
+        const unsigned a_sbo = MMA_A_CHUNKS * 128, b_sbo = MMA_B_CHUNKS * 128;
+        const unsigned long long a_desc0 = umma_desc(smem_addr(s_a), 128, a_sbo);
+        const unsigned long long b_desc0 = umma_desc(smem_addr(s_w), 128, b_sbo);
+        const unsigned b_blk_units = (unsigned)(bsv / 8) * (b_sbo / 16);          // descriptor units per block of support vectors
+        long long iss_tile = blockIdx.x + (long long)s * gridDim.x;
+        unsigned iss_i = (unsigned)s, iss_use = 0, iss_stage = (unsigned)s % MMA_A_STAGES, iss_phase = 0;   // phase of a_full[iss_stage]
+        int iss_blk = 0;
+        bool iss_ext = false;
+        auto issue_next = [&]() {
+            if (iss_tile >= n_tiles) return;
+            if (iss_blk == 0) {
+                MMA_TRACE_WAIT(8, mbar_wait(bar(B_AFULL + iss_stage), iss_phase));
+                iss_ext = (s_ext[iss_stage * 4 + 0] | s_ext[iss_stage * 4 + 1] | s_ext[iss_stage * 4 + 2] | s_ext[iss_stage * 4 + 3]) != 0;
+            }
+            tc_fence_after();
+            const unsigned reg = iss_use & 1u;
+            const unsigned d = tmem_base + (2u * s + reg) * MMA_REGION_COLS;
+            const unsigned long long a0 = a_desc0 + iss_stage * (MMA_A_STAGE_BYTES / 16);
+            const unsigned long long b0 = b_desc0 + (unsigned)iss_blk * b_blk_units;
+            // a K-step takes two adjacent 16-byte chunks of each operand (chunks are 128 bytes = 8 descriptor units apart).
+            // A chunks  H0 H1 H2 0 | M0 M1 M2 0 | L0 L1 L2 0      B chunks  WL0 WL1 WL2 WM0 WM1 WM2 WH0 WH1 WH2 0
+            // The second chunk of the (H2 0) steps is zero on the A side, so whatever follows on the B side does not matter.
+            // Smallest products first.
+            if (iss_ext) {
+                umma_bf16(d, a0 + 8 * 8, b0 + 6 * 8, idesc, 0u);              // (L0 L1).(WH0 WH1)        2^-16
+                umma_bf16(d, a0 + 10 * 8, b0 + 8 * 8, idesc, 1u);             // (L2 0).(WH2 .)
+                umma_bf16(d, a0 + 4 * 8, b0 + 3 * 8, idesc, 1u);              // (M0 M1).(WM0 WM1)        2^-16
+                umma_bf16(d, a0 + 6 * 8, b0 + 5 * 8, idesc, 1u);              // (M2 0).(WM2 .)
+                umma_bf16(d, a0 + 4 * 8, b0 + 6 * 8, idesc, 1u);              // (M0 M1).(WH0 WH1)        2^-8
+                umma_bf16(d, a0 + 6 * 8, b0 + 8 * 8, idesc, 1u);              // (M2 0).(WH2 .)
+            }
+            umma_bf16(d, a0 + 0 * 8, b0 + 0 * 8, idesc, iss_ext ? 1u : 0u);   // (H0 H1).(WL0 WL1)        2^-16
+            umma_bf16(d, a0 + 2 * 8, b0 + 2 * 8, idesc, 1u);                  // (H2 0).(WL2 .)
+            umma_bf16(d, a0 + 0 * 8, b0 + 3 * 8, idesc, 1u);                  // (H0 H1).(WM0 WM1)        2^-8
+            umma_bf16(d, a0 + 2 * 8, b0 + 5 * 8, idesc, 1u);                  // (H2 0).(WM2 .)
+            umma_bf16(d, a0 + 0 * 8, b0 + 6 * 8, idesc, 1u);                  // (H0 H1).(WH0 WH1)        1
+            umma_bf16(d, a0 + 2 * 8, b0 + 8 * 8, idesc, 1u);                  // (H2 0).(WH2 .)
+            tc_commit(bar(B_ACCFULL + 2 * s + reg));
+            ++iss_use;
+            if (++iss_blk == nb) {                                        // the tile's A stage is free once these MMAs are done
+                tc_commit(bar(B_AEMPTY + iss_stage));
+                iss_blk = 0;
+                iss_tile += 2LL * gridDim.x;
+                // the stream's next tile is two further on in the CTA's sequence: stage (i + 2) % 3, and the phase of that
+                // stage's barrier flips every third tile
+                iss_i += 2;
+                iss_stage = iss_i % MMA_A_STAGES;
+                iss_phase = (iss_i / MMA_A_STAGES) & 1u;
+            }
+        };
+        if (issuer) { issue_next(); issue_next(); }
+        __syncwarp();
+#ifdef HFE_MMA_TRACE
+        const long long t_loop0 = clock64();
+#endif
         long long j = 0;
         for (long long i = s, tile = blockIdx.x + (long long)s * gridDim.x; tile < n_tiles; i += 2, tile += 2LL * gridDim.x, ++j) {
             float acc_hi = 0.f, acc_lo = 0.f; // two-float accumulator (error-free TwoSum): keeps the float64 pipe out of the hot loop
@@ -399,7 +466,7 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
             for (int blk = 0; blk < nb; ++blk) {
                 const long long use = j * nb + blk;                  // this stream's running count of blocks
                 const int reg = (int)(use & 1);
-                mbar_wait(bar(B_ACCFULL + 2 * s + reg), (unsigned)((use >> 1) & 1));
+                MMA_TRACE_WAIT(blk < 7 ? blk : 7, mbar_wait(bar(B_ACCFULL + 2 * s + reg), (unsigned)((use >> 1) & 1)));
                 tc_fence_after();
                 const unsigned taddr = lane_base + (unsigned)((2 * s + reg) * MMA_REGION_COLS);
                 const float4* coef4 = reinterpret_cast<const float4*>(s_coef + blk * bsv);
@@ -437,10 +504,15 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
                 } else {
                     lin_dot = vb[15];
                 }
-                // this region may be overwritten by the MMAs of the block after next
+                // this region may be overwritten: once all four warps have said so, the issuer refills it with the block two ahead
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(bar(B_ACCEMPTY + 2 * s + reg));
+                if (issuer) {
+                    MMA_TRACE_WAIT(9, mbar_wait(bar(B_ACCEMPTY + 2 * s + reg), (unsigned)((use >> 1) & 1)));
+                    MMA_TRACE_WAIT(10, issue_next());
+                }
+                __syncwarp();
             }
             // hand the row's sum to the producer thread that finishes it
             ring_sum((int)(i % MMA_RING))[row_in_tile] = widen_f32(acc_hi) + widen_f32(acc_lo);
@@ -448,54 +520,13 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
             __syncwarp();
             if (lane == 0) mbar_arrive(bar(B_SUMFULL + (int)(i % MMA_RING)));
         }
-    } else {
-        // =========================== MMA issuers: one lane per stream =============================================================
-        const int s = warp - MMA_ISSUE_WARP0;
-        if (lane == 0) {
-            mbar_wait(bar(B_W), 0);
-            // instruction descriptor (cute::UMMA::InstrDescriptor): D float32, A and B bfloat16, both K-major, N = bsv, M = 128
-            const unsigned idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((unsigned)(bsv >> 3) << 17) | ((128u >> 4) << 24);
-            const unsigned a_sbo = MMA_A_CHUNKS * 128, b_sbo = MMA_B_CHUNKS * 128;
-            long long j = 0;
-            for (long long i = s, tile = blockIdx.x + (long long)s * gridDim.x; tile < n_tiles; i += 2, tile += 2LL * gridDim.x, ++j) {
-                const int stage = (int)(i % MMA_A_STAGES);
-                mbar_wait(bar(B_AFULL + stage), (unsigned)((i / MMA_A_STAGES) & 1));
-                const bool ext = (s_ext[stage * 4 + 0] | s_ext[stage * 4 + 1] | s_ext[stage * 4 + 2] | s_ext[stage * 4 + 3]) != 0;
-                const unsigned a_base = smem_addr(s_a + stage * MMA_A_STAGE_BYTES);
-#pragma unroll 1
-                for (int blk = 0; blk < nb; ++blk) {
-                    const long long use = j * nb + blk;
-                    const int reg = (int)(use & 1);
-                    mbar_wait(bar(B_ACCEMPTY + 2 * s + reg), (unsigned)(((use >> 1) & 1) ^ 1));
-                    tc_fence_after();
-                    const unsigned d = tmem_base + (unsigned)((2 * s + reg) * MMA_REGION_COLS);
-                    const unsigned b_base = smem_addr(s_w) + (unsigned)(blk * (bsv / 8)) * b_sbo;
-                    auto a_desc = [&](int ks) { return umma_desc(a_base + ks * 256, 128, a_sbo); };
-                    auto b_desc = [&](int chunk, int lbo_chunks) { return umma_desc(b_base + chunk * 128, lbo_chunks * 128, b_sbo); };
-                    // B chunks  WL0 WL1 WL2 WM0 WM1 WM2 WH0 WH1 WH2 0.  Smallest products first.
-                    if (ext) {
-                        // A extension chunks  L0 L1 | M0 L2 | M1 M2 | M0 M1 | M2 0
-                        umma_bf16(d, a_desc(5), b_desc(6, 1), idesc, 0u);         // (L0 L1).(WH0 WH1)        2^-16
-                        umma_bf16(d, a_desc(6), b_desc(3, 5), idesc, 1u);         // (M0 L2).(WM0 WH2)        2^-16
-                        umma_bf16(d, a_desc(7), b_desc(4, 1), idesc, 1u);         // (M1 M2).(WM1 WM2)        2^-16
-                        umma_bf16(d, a_desc(8), b_desc(6, 1), idesc, 1u);         // (M0 M1).(WH0 WH1)        2^-8
-                        umma_bf16(d, a_desc(9), b_desc(8, 1), idesc, 1u);         // (M2 0).(WH2 0)           2^-8
-                    }
-                    // A base chunks  H0 H1 | H2 H0 | H1 H2 | H0 H1 | H2 0
-                    umma_bf16(d, a_desc(0), b_desc(0, 1), idesc, ext ? 1u : 0u);  // (H0 H1).(WL0 WL1)        2^-16
-                    umma_bf16(d, a_desc(1), b_desc(2, 1), idesc, 1u);             // (H2 H0).(WL2 WM0)
-                    umma_bf16(d, a_desc(2), b_desc(4, 1), idesc, 1u);             // (H1 H2).(WM1 WM2)        2^-8
-                    umma_bf16(d, a_desc(3), b_desc(6, 1), idesc, 1u);             // (H0 H1).(WH0 WH1)        1
-                    umma_bf16(d, a_desc(4), b_desc(8, 1), idesc, 1u);             // (H2 0).(WH2 0)
-                    tc_commit(bar(B_ACCFULL + 2 * s + reg));
-                }
-                tc_commit(bar(B_AEMPTY + stage));
-            }
-        }
+#ifdef HFE_MMA_TRACE
+        if (lane == 0) atomicAdd(&g_mma_trace[14], (unsigned long long)(clock64() - t_loop0));
+#endif
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == MMA_ISSUE_WARP0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512));
+    if (warp == MMA_EPI_WARP0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512));
 }
 
 }  // namespace hfe

@@ -27,7 +27,7 @@ __device__ __forceinline__ unsigned long long make_desc(unsigned addr, unsigned 
 }
 
 __global__ void __launch_bounds__(128) probe_kernel(const unsigned char* a_img, const unsigned char* b_img, float* d_out,
-                                                    int n_cols, int ksteps, int nc, int mode, int* err) {
+                                                    int n_cols, int ksteps, int nc, int mode, int* err, int reps, long long* cycles) {
     extern __shared__ __align__(1024) unsigned char smem[];
     __shared__ __align__(8) unsigned long long mbar;
     __shared__ unsigned tmem_base;
@@ -55,10 +55,12 @@ __global__ void __launch_bounds__(128) probe_kernel(const unsigned char* a_img, 
         const unsigned idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((unsigned)(n_cols >> 3) << 17) | ((128u >> 4) << 24);
         const unsigned lbo = mode == 0 ? 128u : (unsigned)nc * 128u;
         const unsigned sbo = mode == 0 ? (unsigned)nc * 128u : 128u;
+        const long long t_start = clock64();
+        for (int rep = 0; rep < reps; ++rep)
         for (int s = 0; s < ksteps; ++s) {
             const unsigned long long da = make_desc(smem_u32(sa) + s * 256, lbo, sbo);
             const unsigned long long db = make_desc(smem_u32(sb) + s * 256, lbo, sbo);
-            const unsigned acc = s > 0 ? 1u : 0u;
+            const unsigned acc = (s > 0 || rep > 0) ? 1u : 0u;
             asm volatile(
                 "{\n"
                 ".reg .pred p;\n"
@@ -67,6 +69,11 @@ __global__ void __launch_bounds__(128) probe_kernel(const unsigned char* a_img, 
                 "}\n" ::"r"(tbase), "l"(da), "l"(db), "r"(idesc), "r"(acc) : "memory");
         }
         asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&mbar)) : "memory");
+        cycles[0] = clock64() - t_start;          // issue time
+        unsigned done = 0;
+        while (!done)
+            asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\nselp.u32 %0, 1, 0, p;\n}\n" : "=r"(done) : "r"(smem_u32(&mbar)) : "memory");
+        cycles[1] = clock64() - t_start;          // issue -> completion visible on the mbarrier
     }
     // wait for the MMAs (bounded spin: a wrong descriptor must not hang the box)
     {
@@ -112,6 +119,7 @@ int main(int argc, char** argv) {
     const int ksteps = argc > 2 ? atoi(argv[2]) : 5;
     const int mode = argc > 3 ? atoi(argv[3]) : 0;
     const int test = argc > 4 ? atoi(argv[4]) : 0;          // 0: random small values; 1: accumulation-precision pattern
+    const int reps = argc > 5 ? atoi(argv[5]) : 1;
     const int nc = 2 * ksteps, K = 8 * nc;
     std::vector<float> A(128 * K), B((size_t)n_cols * K);
     srand(7);
@@ -138,21 +146,26 @@ int main(int argc, char** argv) {
     unsigned char *da, *db;
     float* dd;
     int* derr;
+    long long* dcyc;
     CK(cudaMalloc(&da, ia.size()));
     CK(cudaMalloc(&db, ib.size()));
     CK(cudaMalloc(&dd, sizeof(float) * 128 * n_cols));
     CK(cudaMalloc(&derr, 4));
+    CK(cudaMalloc(&dcyc, 16));
     CK(cudaMemset(derr, 0, 4));
     CK(cudaMemset(dd, 0xFF, sizeof(float) * 128 * n_cols));
     CK(cudaMemcpy(da, ia.data(), ia.size(), cudaMemcpyHostToDevice));
     CK(cudaMemcpy(db, ib.data(), ib.size(), cudaMemcpyHostToDevice));
     size_t smem = ((ia.size() + 1023) & ~1023) + ib.size() + 1024;
     CK(cudaFuncSetAttribute(probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    probe_kernel<<<1, 128, smem>>>(da, db, dd, n_cols, ksteps, nc, mode, derr);
+    probe_kernel<<<1, 128, smem>>>(da, db, dd, n_cols, ksteps, nc, mode, derr, reps, dcyc);
     CK(cudaGetLastError());
     CK(cudaDeviceSynchronize());
     int err = 0;
     CK(cudaMemcpy(&err, derr, 4, cudaMemcpyDeviceToHost));
+    long long cyc[2];
+    CK(cudaMemcpy(cyc, dcyc, 16, cudaMemcpyDeviceToHost));
+    printf("reps=%d: issue %lld clk, issue->complete %lld clk = %.1f clk per MMA instruction\n", reps, cyc[0], cyc[1], (double)cyc[1] / (reps * ksteps));
     std::vector<float> D(128 * n_cols);
     CK(cudaMemcpy(D.data(), dd, D.size() * 4, cudaMemcpyDeviceToHost));
     double max_abs = 0, max_rel = 0;
