@@ -79,8 +79,16 @@ __device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+// tcgen05.commit / tcgen05.mma are executed by a converged warp; one elected lane issues.  (Issued from inside a divergent
+// `if (lane == 0)` the compiler wraps every operand in an elect / broadcast loop to get it into uniform registers, which
+// made six small MMAs cost ~900 clocks.)
 __device__ __forceinline__ void tc_commit(unsigned bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+    asm volatile(
+        "{\n"
+        ".reg .pred q;\n"
+        "elect.sync _|q, 0xffffffff;\n"
+        "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n"
+        "}\n" ::"r"(bar) : "memory");
 }
 // shared-memory matrix descriptor: K-major, no swizzle; LBO = bytes between the two 16-byte K chunks of one K-step,
 // SBO = bytes between 8-row groups (cute::UMMA::SmemDescriptor: start [0,14), LBO [16,30), SBO [32,46), version 1 at 46)
@@ -92,9 +100,10 @@ __device__ __forceinline__ void umma_bf16(unsigned d_tmem, unsigned long long da
                                           unsigned accumulate) {
     asm volatile(
         "{\n"
-        ".reg .pred p;\n"
+        ".reg .pred p, q;\n"
+        "elect.sync _|q, 0xffffffff;\n"
         "setp.ne.b32 p, %4, 0;\n"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+        "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
         "}\n" ::"r"(d_tmem), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
 }
 // 16 consecutive float32 columns of this thread's TMEM lane
@@ -165,7 +174,8 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
     volatile unsigned* s_tmem = s_misc;                    // TMEM base address
     volatile unsigned* s_ext = s_misc + 4;                 // [stage][producer warp]: tile needs the extension block
 
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int warp = __shfl_sync(0xFFFFFFFFu, tid >> 5, 0);          // tells the compiler that the warp index is warp-uniform
     const long long n_tiles = (P.n + MMA_TILE_ROWS - 1) / MMA_TILE_ROWS;
     const int nb = Q.nb, bsv = Q.block_sv;
 
@@ -397,9 +407,11 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
         mbar_wait(bar(B_W), 0);
         const float* s_coef = reinterpret_cast<const float*>(s_w + (size_t)nb * bsv * (MMA_B_CHUNKS * 16));
         const int steps = bsv >> 4;
-        // ---- MMA issue: lane 0 of the stream's first warp.  Blocks of the stream's tiles are issued in order, each into the
+        // ---- MMA issue, in turn by the four warps of the stream (converged; one elected lane issues): block u is issued by
+        //      warp u % 4.  A fixed issuer would fall behind its three peers by the issue time in every block and they would wait
+        //      for it; taking turns, every warp is late once in four blocks and the two-region pipeline absorbs it.  Blocks of the stream's tiles are issued in order, each into the
         //      region the four warps have just drained (the first two go into the still empty regions). ----------------------
-        const bool issuer = ((warp & 3) == 0) && lane == 0;
+        const unsigned quarter = (unsigned)warp & 3u;
         // instruction descriptor (cute::UMMA::InstrDescriptor): D float32, A and B bfloat16, both K-major, N = bsv, M = 128
         const unsigned idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((unsigned)(bsv >> 3) << 17) | ((128u >> 4) << 24);
         // descriptors are built once; per instruction only the 14-bit start-address field (16-byte units, low word) moves
@@ -411,12 +423,11 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
         unsigned iss_i = (unsigned)s, iss_use = 0, iss_stage = (unsigned)s % MMA_A_STAGES, iss_phase = 0;   // phase of a_full[iss_stage]
         int iss_blk = 0;
         bool iss_ext = false;
-        auto issue_next = [&]() {
+        auto issue_next = [&](bool mine) {           // every warp of the stream keeps the issue state; `mine` issues
             if (iss_tile >= n_tiles) return;
-            if (iss_blk == 0) {
-                MMA_TRACE_WAIT(8, mbar_wait(bar(B_AFULL + iss_stage), iss_phase));
-                iss_ext = (s_ext[iss_stage * 4 + 0] | s_ext[iss_stage * 4 + 1] | s_ext[iss_stage * 4 + 2] | s_ext[iss_stage * 4 + 3]) != 0;
-            }
+            if (mine) {
+            MMA_TRACE_WAIT(8, mbar_wait(bar(B_AFULL + iss_stage), iss_phase));
+            iss_ext = (s_ext[iss_stage * 4 + 0] | s_ext[iss_stage * 4 + 1] | s_ext[iss_stage * 4 + 2] | s_ext[iss_stage * 4 + 3]) != 0;
             tc_fence_after();
             const unsigned reg = iss_use & 1u;
             const unsigned d = tmem_base + (2u * s + reg) * MMA_REGION_COLS;
@@ -441,9 +452,16 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
             umma_bf16(d, a0 + 0 * 8, b0 + 6 * 8, idesc, 1u);                  // (H0 H1).(WH0 WH1)        1
             umma_bf16(d, a0 + 2 * 8, b0 + 8 * 8, idesc, 1u);                  // (H2 0).(WH2 .)
             tc_commit(bar(B_ACCFULL + 2 * s + reg));
-            ++iss_use;
-            if (++iss_blk == nb) {                                        // the tile's A stage is free once these MMAs are done
+            if (iss_blk + 1 == nb) {
+                // The tile's A stage is free once its MMAs are done.  A commit only tracks the MMAs of the committing thread, and
+                // the tile's earlier blocks were issued by the other warps: all but the previous one have already been consumed,
+                // so wait for that one's completion and then commit for this block.
+                if (iss_use > 0) mbar_wait(bar(B_ACCFULL + 2 * s + (reg ^ 1u)), ((iss_use - 1) >> 1) & 1u);
                 tc_commit(bar(B_AEMPTY + iss_stage));
+            }
+            }
+            ++iss_use;
+            if (++iss_blk == nb) {
                 iss_blk = 0;
                 iss_tile += 2LL * gridDim.x;
                 // the stream's next tile is two further on in the CTA's sequence: stage (i + 2) % 3, and the phase of that
@@ -453,7 +471,8 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
                 iss_phase = (iss_i / MMA_A_STAGES) & 1u;
             }
         };
-        if (issuer) { issue_next(); issue_next(); }
+        issue_next(quarter == 0);
+        issue_next(quarter == 1);
         __syncwarp();
 #ifdef HFE_MMA_TRACE
         const long long t_loop0 = clock64();
@@ -508,9 +527,10 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(bar(B_ACCEMPTY + 2 * s + reg));
-                if (issuer) {
-                    MMA_TRACE_WAIT(9, mbar_wait(bar(B_ACCEMPTY + 2 * s + reg), (unsigned)((use >> 1) & 1)));
-                    MMA_TRACE_WAIT(10, issue_next());
+                {
+                    const bool mine = ((unsigned)(use + 2) & 3u) == quarter;
+                    if (mine) MMA_TRACE_WAIT(9, mbar_wait(bar(B_ACCEMPTY + 2 * s + reg), (unsigned)((use >> 1) & 1)));
+                    MMA_TRACE_WAIT(10, issue_next(mine));
                 }
                 __syncwarp();
             }
