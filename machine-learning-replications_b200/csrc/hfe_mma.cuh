@@ -220,9 +220,9 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
             if (P.perm_col >= 0) {                             // a permutation-importance pass: one column through the index
                 const int src = __ldg(P.perm_idx + row_ld);
                 HFE_ASSERT_IN(src >= 0 && src < P.n);
+                const float xp = __ldg(P.x + P.col_off[P.perm_col] + src);
 #pragma unroll
-                for (int f = 0; f < F; ++f)
-                    if (f == P.perm_col) x[f] = __ldg(P.x + P.col_off[f] + src);
+                for (int f = 0; f < F; ++f) x[f] = (f == P.perm_col) ? xp : x[f];    // selects: x[] must stay in registers
             }
         };
         float xn[F];
@@ -251,34 +251,30 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
             }
             const bool fix_row = valid && (nonfinite || !(sum_abs * Q.wmax_all <= 96.f));
             const bool keep = valid && !fix_row;
-            // bfloat16 hi parts, two features per conversion; what one bfloat16 cannot carry stays in rem
+            // bfloat16 hi parts, two features per conversion; is there anything one bfloat16 cannot carry?
             unsigned hp[9];
 #pragma unroll
             for (int k = 0; k < 8; ++k) hp[k] = pack_bf16(xc[2 * k], xc[2 * k + 1]);
             hp[8] = pack_bf16(xc[16], 0.f);
-            float rem[F];
             unsigned rem_bits = 0;
 #pragma unroll
             for (int f = 0; f < F; ++f) {
                 const float hi = __uint_as_float((f & 1) ? (hp[f >> 1] & 0xFFFF0000u) : (hp[f >> 1] << 16));
-                rem[f] = xc[f] - hi;
-                rem_bits |= __float_as_uint(rem[f]);
+                rem_bits |= __float_as_uint(xc[f] - hi);
             }
             const bool inexact = keep && (rem_bits << 1) != 0;
-            if (!keep) {                                   // keeps NaN / Inf (and rows beyond n) out of the tensor core
-#pragma unroll
-                for (int k = 0; k < 9; ++k) hp[k] = 0u;
-            }
-            // boosted stumps: the raw score goes to the thread's later self through the ring, links are evaluated there
+            // boosted stumps: the raw score goes to the finishing warps through the ring, the links are evaluated there
             float raw32 = 0.f;
             if (TREE_MODE == 1) {
-                float acc[1] = {0.f};
 #pragma unroll
                 for (int f = 0; f < F; ++f) {
-                    const float xf[1] = {x[f]};
-                    apply_splits<1>(P, f, xf, acc);
+                    if (x[f] <= P.split1_thr[f]) raw32 += P.split1_delta[f];
+                    if ((Q.extra_split_mask >> f) & 1u) {              // further splits of this feature (warp-uniform, rare)
+#pragma unroll 1
+                        for (int sp = P.split_begin[f]; sp < P.split_begin[f + 1]; ++sp)
+                            if (x[f] <= P.split_thr[sp]) raw32 += P.split_delta[sp];
+                    }
                 }
-                raw32 = acc[0];
             }
             if (nonfinite) atomicOr(P.status, HFE_ROW_NONFINITE);
             // what the finishing warps need besides the RBF sum (they have released slot i % 8 of the ring after tile i - 8)
@@ -291,18 +287,20 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
             // of the centred features; the zero chunks are never written).  Only tiles holding a value that one bfloat16
             // cannot carry use the mid / lo chunks, but then the rows of all four warps must be there.
             unsigned char* a_row = s_a + stage * MMA_A_STAGE_BYTES + (prow >> 3) * (MMA_A_CHUNKS * 128) + (prow & 7) * 16;
-            *reinterpret_cast<uint4*>(a_row + 0 * 128) = make_uint4(hp[0], hp[1], hp[2], hp[3]);
-            *reinterpret_cast<uint4*>(a_row + 1 * 128) = make_uint4(hp[4], hp[5], hp[6], hp[7]);
-            *reinterpret_cast<uint4*>(a_row + 2 * 128) = make_uint4(hp[8], 0u, 0u, 0u);
+            const unsigned km = keep ? 0xFFFFFFFFu : 0u;     // keeps NaN / Inf (and rows beyond n) out of the tensor core
+            *reinterpret_cast<uint4*>(a_row + 0 * 128) = make_uint4(hp[0] & km, hp[1] & km, hp[2] & km, hp[3] & km);
+            *reinterpret_cast<uint4*>(a_row + 1 * 128) = make_uint4(hp[4] & km, hp[5] & km, hp[6] & km, hp[7] & km);
+            *reinterpret_cast<uint4*>(a_row + 2 * 128) = make_uint4(hp[8] & km, 0u, 0u, 0u);
             const bool ext = __any_sync(0xFFFFFFFFu, inexact);
-            if (!keep) {
-#pragma unroll
-                for (int f = 0; f < F; ++f) rem[f] = 0.f;
-            }
             uint4 m0 = make_uint4(0, 0, 0, 0), m1 = m0, m2 = m0, l0 = m0, l1 = m0, l2 = m0;
             if (ext) {
                 unsigned mp[9];
-                float lo[F];
+                float rem[F], lo[F];
+#pragma unroll
+                for (int f = 0; f < F; ++f) {
+                    const float hi = __uint_as_float((f & 1) ? (hp[f >> 1] & 0xFFFF0000u) : (hp[f >> 1] << 16));
+                    rem[f] = keep ? (x[f] - Q.center[f]) - hi : 0.f;
+                }
 #pragma unroll
                 for (int k = 0; k < 8; ++k) mp[k] = pack_bf16(rem[2 * k], rem[2 * k + 1]);
                 mp[8] = pack_bf16(rem[16], 0.f);

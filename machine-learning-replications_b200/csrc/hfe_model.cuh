@@ -137,6 +137,7 @@ struct MmaParams {
     float center[F];                // m_d: the scaler mean rounded to an integer
     float zz_a[F], zz_b[F];         // |z|^2 = sum_d xc_d (a_d xc_d + b_d) + c,  xc = x - m
     float zz_c;
+    unsigned extra_split_mask;      // bit f: feature f has more than one merged stump split
     float wmax_all;                 // max_dj |W_dj| (slightly enlarged): |exponent of a row| <= wmax_all * sum_d |xc_d|
     double lin_base;                // logistic member: intercept + sum_d m_d * coef_d; the dot product over x - m is the last
                                     // column of the B operand (coefficient 0 in the RBF sum) and comes off the tensor core
@@ -870,6 +871,10 @@ inline int build_model(const uint8_t* blob, size_t len, int device, Model** out)
             // last column of the B operand; that column's RBF coefficient is zero
             MmaParams& Q = m->mma;
             Q.lin_base = P.lin_intercept;
+            Q.extra_split_mask = 0;
+            if (m->tree_mode == 1)
+                for (int d = 0; d < F; ++d)
+                    if (P.split_begin[d + 1] != P.split_begin[d]) Q.extra_split_mask |= 1u << d;
             const int col = Q.nb * Q.block_sv - 1;
             uint16_t* row = reinterpret_cast<uint16_t*>(m->mma_img_host.data() + (size_t)(col / 8) * (MMA_B_CHUNKS * 128) + (col % 8) * 16);
             for (int d = 0; d < F; ++d) {
