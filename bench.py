@@ -433,6 +433,8 @@ def run_ours(args):
     torch.cuda.set_device(local_rank)
     ctx = Ctx(pkg, torch, rank, local_rank, world)
     clf = pkg.HFStackB200.from_arrays(arrays, device=local_rank)
+    if int(clf.info.n_support_vectors):
+        clf.set_rbf_engine(args.engine)
     if args.rows:
         n_total, scaling = int(args.rows) * world, "weak"
     else:
@@ -533,7 +535,20 @@ def run_ours(args):
                      "note": ("the RBF-SVC member makes this pass FP32-FMA / MUFU bound, not HBM bound: see fma_roofline"
                               if n_sv else "no SVC member: this configuration is the HBM-bound part of the ensemble")},
     }
-    if n_sv:
+    engine = int(clf.info.rbf_engine)
+    line["config"]["rbf_engine"] = {0: "none (no SVC member)", 1: "simt (FFMA2 loop)", 2: "tensor cores (tcgen05.mma + TMEM)"}[engine]
+    if engine == 2:
+        # the tensor-core engine leaves one exponential per (row, support-vector column) on the MUFU pipe, and as many
+        # float32 values to read back from TMEM: both paths move 16 per clock and SM
+        exps = int(clf.info.rbf_exp_per_row)
+        peak = sms * 16 * sm_mhz * 1e6
+        line["roofline"]["kernel"] = "hfe_mma_kernel (tcgen05 RBF contraction + MUFU epilogue; the fix-up launch that follows takes microseconds)"
+        line["roofline"]["note"] = "the RBF-SVC member makes this pass MUFU / TMEM-read bound, not HBM bound: see mufu_roofline"
+        line["mufu_roofline"] = {"bound": "MUFU.EX2 pipe = TMEM read path (16 values per clock and SM)",
+                                 "achieved": exps * n / (avg_launch_ms * 1e-3) / 1e12, "peak": peak / 1e12,
+                                 "unit": "T exp/s", "frac": exps * n / (avg_launch_ms * 1e-3) / peak,
+                                 "exp_per_row": exps, "sm_mhz_used": sm_mhz, "sms": sms}
+    if n_sv and engine == 1:
         line["fma_roofline"] = {"bound": "fp32 fma pipe", "achieved": fma_per_row * n / (avg_launch_ms * 1e-3) / 1e12,
                                 "peak": fma_peak / 1e12, "unit": "T lane-FMA/s",
                                 "frac": fma_per_row * n / (avg_launch_ms * 1e-3) / fma_peak,
@@ -568,6 +583,8 @@ def main():
     ap.add_argument("--cpu-rows", type=int, default=0)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--legs", default="all", help="all | none | comma list of svc_free,stress,perm")
+    ap.add_argument("--engine", default="auto", choices=["auto", "simt", "tensor"],
+                    help="what evaluates the RBF sum: tensor cores (tcgen05) or the SIMT FFMA2 loop; auto = tensor when it fits")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

@@ -80,7 +80,7 @@ typedef struct hfe_model_info {
     double  svc_guard;             /* |decision value| uncertainty assumed for the float32 RBF sum */
     uint64_t device_bytes;         /* bytes of device memory the handle owns */
     int32_t rbf_engine;            /* what scores the RBF sum: 0 no SVC member, 1 SIMT FFMA2 loop, 2 tensor cores (tcgen05) */
-    int32_t reserved_;
+    int32_t rbf_exp_per_row;       /* exponentials the active engine evaluates per row (tensor cores: padded column count) */
 } hfe_model_info;
 
 /* Replaces pickle.load('./hf_predict_model.pkl') (predict_hf.py:33-34): validates the flat blob written by
@@ -90,7 +90,8 @@ int hfe_model_create(const void* blob, size_t blob_bytes, int device, hfe_model*
 void hfe_model_destroy(hfe_model* model);
 int hfe_model_get_info(const hfe_model* model, hfe_model_info* out_info);
 /* Which engine evaluates the RBF sum of the SVC member (svm.cpp:461-515, 2821-2904): 0 = automatic (the tensor-core kernel
- * when the model fits it: at most 512 support vectors, no general tree tables), 1 = the SIMT FFMA2 loop, 2 = the
+ * when the model fits it: at most ~460 support vectors -- its operand tables share one SM's shared memory -- and no
+ * general tree tables), 1 = the SIMT FFMA2 loop, 2 = the
  * tensor-core kernel or HFE_ERR_UNSUPPORTED at scoring time.  Both meet the same parity bars; the switch exists so that
  * the two can be measured and tested side by side.  Set it before the handle is shared between threads. */
 int hfe_model_set_rbf_engine(hfe_model* model, int engine);

@@ -38,7 +38,7 @@ class ModelInfo(C.Structure):
         ("n_support_vectors", C.c_int32), ("n_trees", C.c_int32), ("n_tree_nodes", C.c_int32),
         ("max_tree_depth", C.c_int32), ("tree_mode", C.c_int32), ("n_merged_splits", C.c_int32),
         ("device", C.c_int32), ("rbf_fma_per_row", C.c_int32), ("svc_guard", C.c_double), ("device_bytes", C.c_uint64),
-        ("rbf_engine", C.c_int32), ("reserved_", C.c_int32),
+        ("rbf_engine", C.c_int32), ("rbf_exp_per_row", C.c_int32),
     ]
 
 

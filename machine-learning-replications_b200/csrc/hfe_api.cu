@@ -169,7 +169,7 @@ int dispatch_score(const Model* m, const ScoreParams& P, cudaStream_t stream) {
     if (svc && m->mma.nb > 0 && m->tree_mode != 2 && m->rbf_engine != 1)
         return m->tree_mode == 0 ? launch_mma<0>(m, P, stream) : launch_mma<1>(m, P, stream);
     if (svc && m->rbf_engine == 2)
-        return fail(HFE_ERR_UNSUPPORTED, "the tensor-core RBF path needs at most 512 support vectors and no general tree tables");
+        return fail(HFE_ERR_UNSUPPORTED, "the tensor-core RBF path needs at most ~460 support vectors (shared memory) and no general tree tables");
     bool identity = true;                          // the feature order is only changed for stacks with an SVC member
     for (int f = 0; f < F; ++f) identity = identity && m->col_of[f] == f;
     // (tensor-copy coordinates are signed 32-bit: beyond 2^31 rows the register-window instance takes over)
@@ -383,6 +383,7 @@ static void fill_info(const Model* m, hfe_model_info* info) {
     info->svc_guard = m->svc_guard;
     info->device_bytes = m->device_bytes;
     info->rbf_engine = m->n_sv == 0 ? 0 : (m->mma.nb > 0 && m->tree_mode != 2 && m->rbf_engine != 1) ? 2 : 1;
+    info->rbf_exp_per_row = info->rbf_engine == 2 ? m->mma.nb * m->mma.block_sv : ((m->n_sv + 3) / 4) * 4;
 }
 
 int hfe_predict_proba(const hfe_model* model, const float* x, int64_t n, int64_t ld, float* out_n2, uint32_t* status,

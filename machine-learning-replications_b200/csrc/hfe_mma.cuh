@@ -16,20 +16,26 @@
 // row term) stay out of the accumulator, and K-steps run from the smallest parts to the largest, so each accumulation
 // loses at most the float32 rounding of the exponent itself.
 //
-// One persistent CTA per SM, 14 warps:
+// One persistent CTA per SM, 16 warps (512 threads, 128 registers each):
 //   warps 0-3   producers: load the tile's 128 rows (coalesced column reads, the next tile's loads in flight while this
 //               one is processed), centre and split them, write the A operand into shared memory in the canonical
-//               K-major core-matrix layout, evaluate the tree and logistic members; a few tiles later, when the RBF sums
-//               of a tile have come back through shared memory, the same thread finishes its row: Platt + coupling +
-//               combiner (finish_rows_fast), four tiles at a time so that four float64 chains are interleaved
-//   warps 4-7   exponent warps of stream 0, warps 8-11 of stream 1: thread = row (TMEM lane); tcgen05.ld 16 columns at a
-//               time, ex2, coefficient FFMA2, float64 fold -- nothing else, so that the MUFU pipe always has work
-//               lane 0 of the first warp of each stream also issues the stream's tcgen05.mma instructions: as soon as the
-//               four warps have drained a region it refills it with the block two ahead and commits to an mbarrier
+//               K-major core-matrix layout (five stages), evaluate the merged stump splits
+//   warps 4-7   finishing warps: thread = row; when the RBF sums of four consecutive tiles have come back through the
+//               shared-memory ring the thread finishes its four rows together -- links, Platt, clamp, coupling, combiner
+//               (partial_logit_fast / finish_rows_fast, the SIMT kernel's code), four float64 chains interleaved
+//   warps 8-11  exponent warps of stream 0, warps 12-15 of stream 1: thread = row (TMEM lane); tcgen05.ld 16 columns at a
+//               time, ex2, coefficient FFMA2, two-float fold -- nothing else, so that the MUFU pipe always has work.
+//               In turn the four warps of a stream also issue the stream's tcgen05.mma instructions (converged warp,
+//               elect.sync): as soon as a region has been drained it is refilled with the block two ahead.
 // Tiles alternate between the two streams.  Support vectors are taken in blocks of up to 128; TMEM (512 columns) is cut
-// into four regions, two per stream: while a stream's epilogue warps drain one block from one region the tensor core
-// fills the other, and the other stream keeps the MUFU pipe busy in the meantime.  Both the MUFU pipe and the TMEM read
-// path move 16 values per clock and SM: 28 clocks per row for 448 support vectors is the floor of this design.
+// into four regions, two per stream: while a stream's warps drain one block from one region the tensor core fills the
+// other, and the other stream keeps the MUFU pipe busy in the meantime.  The logistic member's dot product rides along as
+// the last column of the B operand.  Both the MUFU pipe and the TMEM read path move 16 values per clock and SM: 28
+// clocks per row for 448 columns is the floor of this design (10.4 G rows/s at 1965 MHz).
+// What was measured on the way (B200, 10 M rows, published model; DESIGN.md section 10 has the table): MMAs issued from
+// a divergent `if (lane == 0)` cost ~150 clocks each (operand broadcast loops); a fixed issuing warp makes its three
+// peers wait for it every block; the float64 epilogue needs four warps of its own (two were the bottleneck, and inside
+// the exponent warps it kept them off the MUFU pipe a quarter of the time).
 #pragma once
 
 #include <cuda_bf16.h>
@@ -48,6 +54,8 @@ constexpr int MMA_A_STAGE_BYTES = (MMA_TILE_ROWS / 8) * MMA_A_CHUNKS * 128;     
 constexpr int MMA_RING = 12;                             // tiles between a row's production and its float64 epilogue
 constexpr int MMA_RING_SLOT_BYTES = MMA_TILE_ROWS * 20;  // per tile and row: RBF sum (f64), logistic dot, stump score, gamma|z|^2 (f32)
 constexpr int MMA_REGION_COLS = 128;                     // TMEM columns per region
+static_assert(MMA_A_STAGES * MMA_A_STAGE_BYTES == 5 * 24576 && MMA_RING * MMA_RING_SLOT_BYTES == 12 * 2560,
+              "hfe_model.cuh sizes the support-vector limit of this kernel from these");
 constexpr int MMA_TAIL_ROWS = 4;                         // tiles whose float64 epilogue one thread runs interleaved
 
 // ---- PTX helpers ---------------------------------------------------------------------------------------------------------

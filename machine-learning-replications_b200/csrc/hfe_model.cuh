@@ -563,6 +563,8 @@ inline int build_svc(Model* m, const ParsedBlob& pb, uint32_t idx) {
             usable = usable && std::isfinite(folded) && std::fabs(bias) <= 100.0;
             coef_tab[col] = (float)folded;
         }
+        // [B image + coefficients | 5 A stages | 12 ring slots | barriers] must fit one block's 227 KB (hfe_mma.cuh)
+        usable = usable && ((mma_img.size() + 1023) & ~(size_t)1023) + 5 * 24576 + 12 * 2560 + 512 <= 227 * 1024;
         if (usable) {
             Q.nb = nb;
             Q.block_sv = bsv;
@@ -912,6 +914,13 @@ inline int build_model(const uint8_t* blob, size_t len, int device, Model** out)
         double w_svc = P.slot_svc >= 0 ? std::fabs(P.final_coef[P.slot_svc]) : 0.0;
         P.label_guard = 2.0 * w_svc * slope * m->svc_guard + 1e-9 +
                         (P.slot_gbt >= 0 ? std::fabs(P.final_coef[P.slot_gbt]) * 0.25 * m->gbt_guard : 0.0);
+        if (m->mma.nb > 0 && P.slot_lin >= 0) {
+            // tensor-core engine: the logistic member's dot product comes out of a float32 accumulator (|error| <~ 2^-23 of
+            // the largest partial sum) instead of a float64 FMA chain
+            double mag = std::fabs(m->mma.lin_base);
+            for (int d = 0; d < F; ++d) mag += 64.0 * std::fabs(P.lin_coef[d]);
+            P.label_guard += std::fabs(P.final_coef[P.slot_lin]) * 0.25 * 1.2e-7 * mag;
+        }
         if (P.slot_svc < 0 && m->tree_mode != 2) {
             // stacks scored by the streaming pass: float32 links (|error| <= 1.8e-7 each) and a float32 combiner logit
             double w_sum = 0.0;

@@ -576,6 +576,118 @@ def test_prefix_shared_support_vector_layout(pkg, published, retrained, torch_cu
         clf.close()
 
 
+def test_tensor_core_engine_against_simt_engine_and_oracle(case, pkg, torch_cuda):
+    """The RBF sum on the tensor cores (tcgen05.mma, TMEM accumulators; hfe_mma.cuh) and on the SIMT FFMA2 loop meet the
+    same bars: probabilities <= 1e-6 against the oracle, labels exact, the two engines within float32 noise of each
+    other -- on schema rows, on values one bfloat16 cannot carry (extension block), with a permuted column, NaN rows,
+    rows far outside the training range (exponent bound -> float64 fix-up), every optional output, ragged sizes."""
+    torch = torch_cuda
+    arrays = case["arrays"]
+    clf = pkg.HFStackB200.from_arrays(arrays)
+    assert clf.info.rbf_engine == 2                                   # automatic choice for the fixture models
+    n = 70_001
+    X = pkg.synth.host_rows(case["specs"], 51, 0, n).astype(np.float64)
+    rng = np.random.default_rng(4)
+    Xf = X + rng.normal(0, 0.41, X.shape) * (rng.random(X.shape) < 0.25)          # fractional values: extension block
+    Xo = X.copy()
+    Xo[::97] *= 9.0                                                                # outliers: exponent bound
+    for name, M in (("schema", X), ("fractional", Xf), ("outliers", Xo)):
+        want = so.predict_proba(arrays, M)
+        want_lab = (so.decision_function(arrays, M) > 0).astype(np.uint8)
+        want_meta = so.transform(arrays, M)
+        x = clf.to_device_colmajor(M)
+        got = {}
+        for eng in ("simt", "tensor"):
+            clf.set_rbf_engine(eng)
+            assert clf.info.rbf_engine == (1 if eng == "simt" else 2)
+            out = torch.empty((n, 2), dtype=torch.float32, device="cuda")
+            lab = torch.empty(n, dtype=torch.uint8, device="cuda")
+            dec = torch.empty(n, dtype=torch.float64, device="cuda")
+            meta = torch.empty((n, 3), dtype=torch.float64, device="cuda")
+            st = clf.score_device(x, n=n, out=out, labels=lab, decision=dec, meta=meta)
+            torch.cuda.synchronize()
+            assert int(st[0].item()) == 0, (name, eng)
+            got[eng] = out.cpu().numpy().astype(np.float64)
+            assert np.abs(got[eng] - want).max() <= PROBA_TOL, (name, eng)
+            assert np.array_equal(lab.cpu().numpy(), want_lab), (name, eng)
+            assert np.abs(meta.cpu().numpy() - want_meta).max() <= 2e-6, (name, eng)
+            assert np.abs(dec.cpu().numpy() - so.decision_function(arrays, M)).max() <= 5e-6, (name, eng)
+            for m in (1, 127, 128, 129, 4099):                           # ragged tiles
+                o = clf.predict_proba_device(x[:, :((m + 3) & ~3)].contiguous(), n=m)
+                torch.cuda.synchronize()
+                assert np.abs(o.cpu().numpy() - want[:m]).max() <= PROBA_TOL, (name, eng, m)
+        assert np.abs(got["simt"] - got["tensor"]).max() <= 6e-7, name
+    clf.set_rbf_engine("tensor")
+    # a permuted column and the on-device accuracy count
+    perm = np.random.RandomState(5).permutation(n).astype(np.int32)
+    col = 13
+    Xp = X.copy()
+    Xp[:, col] = X[perm, col]
+    x, xp = clf.to_device_colmajor(X), clf.to_device_colmajor(Xp)
+    y = (so.decision_function(arrays, Xp) > 0).astype(np.uint8)
+    out_a = torch.empty((n, 2), dtype=torch.float32, device="cuda")
+    out_b = torch.empty_like(out_a)
+    score = torch.zeros(1, dtype=torch.int64, device="cuda")
+    clf.score_device(x, n=n, perm_col=col, perm_idx=torch.from_numpy(perm).cuda(), out=out_a, y=torch.from_numpy(y).cuda(),
+                     score=score)
+    clf.score_device(xp, n=n, out=out_b)
+    torch.cuda.synchronize()
+    assert torch.equal(out_a, out_b) and int(score.item()) == n
+    # NaN / Inf rows are flagged and come out as NaN, their neighbours are untouched
+    bad = X[:1000].copy()
+    bad[77, 5] = np.nan
+    bad[500, 16] = np.inf
+    xb = clf.to_device_colmajor(bad)
+    st = clf.new_status()
+    ob = clf.predict_proba_device(xb, n=1000, status=st)
+    torch.cuda.synchronize()
+    assert int(st[0].item()) & pkg.capi.ROW_NONFINITE
+    assert torch.isnan(ob[77]).all() and torch.isnan(ob[500]).all()
+    keep = np.setdiff1d(np.arange(1000), [77, 500])
+    assert np.abs(ob.cpu().numpy()[keep] - so.predict_proba(arrays, X[:1000])[keep]).max() <= PROBA_TOL
+    clf.close()
+
+
+def test_tensor_core_engine_table_shapes(pkg, published, torch_cuda):
+    """Support-vector counts around the block boundaries of the tensor-core kernel (1 to 4 blocks of up to 128 columns,
+    the spare logistic column), the shared-memory limit (falls back to the SIMT loop), stacks without a logistic or a
+    boosting member."""
+    import copy
+    rng = np.random.default_rng(17)
+    base = published["arrays"]
+    X = pkg.synth.host_rows(published["specs"], 61, 0, 9000).astype(np.float64)
+
+    def with_svs(n_sv):
+        arrays = copy.deepcopy(base)
+        svc = arrays.members[0]
+        pick = rng.integers(0, svc.sv.shape[0], n_sv)
+        svc.sv = svc.sv[pick] + rng.normal(0, 0.05, (n_sv, 17))
+        svc.dual_coef = svc.dual_coef[pick] * min(434.0 / n_sv, 4.0)
+        order = np.argsort(svc.dual_coef > 0, kind="stable")
+        svc.sv, svc.dual_coef = svc.sv[order], svc.dual_coef[order]
+        n0 = int((svc.dual_coef <= 0).sum())
+        svc.n_support = np.array([n0, n_sv - n0])
+        return arrays
+
+    for n_sv, engine in ((1, 2), (15, 2), (16, 2), (127, 2), (128, 2), (129, 2), (255, 2), (256, 2), (383, 2), (447, 2),
+                         (448, 1), (600, 1)):
+        arrays = with_svs(n_sv)
+        clf = pkg.HFStackB200.from_arrays(arrays)
+        assert clf.info.rbf_engine == engine, n_sv
+        dev, lab = device_scores(clf, X)
+        assert np.abs(dev - so.predict_proba(arrays, X)).max() <= PROBA_TOL, n_sv
+        assert np.array_equal(arrays.classes[lab], so.predict(arrays, X)), n_sv
+        clf.close()
+    wm = pkg.synth_models.without_member
+    for arrays in (wm(base, "linear"), wm(base, "gbt"), wm(wm(base, "gbt"), "linear")):
+        clf = pkg.HFStackB200.from_arrays(arrays)
+        assert clf.info.rbf_engine == 2
+        dev, lab = device_scores(clf, X)
+        assert np.abs(dev - so.predict_proba(arrays, X)).max() <= PROBA_TOL
+        assert np.array_equal(arrays.classes[lab], so.predict(arrays, X))
+        clf.close()
+
+
 def test_streaming_pass_for_stacks_without_svc(pkg, published, retrained, torch_cuda):
     """Stacks without the SVC member go through hfe_stream_kernel (TMA-staged tiles, float32 links): same bars --
     probabilities <= 1e-6, labels and leaves bit-exact -- at ragged sizes, with a permuted column, NaN rows and the
