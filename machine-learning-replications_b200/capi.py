@@ -20,7 +20,7 @@ NOALLOC_MAX_ROWS = 1 << 26
 METRIC_BINS = 65536
 
 EXPORTS = [
-    "hfe_abi_version", "hfe_last_error_string", "hfe_model_create", "hfe_model_destroy", "hfe_model_get_info", "hfe_model_plan", "hfe_model_set_rbf_engine",
+    "hfe_abi_version", "hfe_last_error_string", "hfe_model_create", "hfe_model_destroy", "hfe_model_get_info", "hfe_model_plan", "hfe_model_set_rbf_engine", "hfe_model_set_tree_engine",
     "hfe_predict_proba", "hfe_predict", "hfe_score", "hfe_apply", "hfe_predict_proba_f64", "hfe_score_f64", "hfe_synth_rows",
     "hfe_ingest_rowmajor_f64", "hfe_ingest_rowmajor_f32", "hfe_ingest_rowmajor_i64", "hfe_ingest_rowmajor_u8", "hfe_knn1_impute", "hfe_predict_host", "hfe_predict_proba_noalloc", "hfe_binary_metrics",
 ]
@@ -63,6 +63,7 @@ def load_library(path: str = LIB_PATH):
     lib.hfe_model_destroy.restype = None
     lib.hfe_model_get_info.argtypes = [vp, C.POINTER(ModelInfo)]
     lib.hfe_model_set_rbf_engine.argtypes = [vp, C.c_int]
+    lib.hfe_model_set_tree_engine.argtypes = [vp, C.c_int]
     lib.hfe_model_plan.argtypes = [vp, C.c_size_t, C.POINTER(ModelInfo), C.POINTER(C.c_int32)]
     lib.hfe_predict_proba.argtypes = [vp, vp, i64, i64, vp, vp, vp]
     lib.hfe_predict.argtypes = [vp, vp, i64, i64, vp, vp, vp, vp]

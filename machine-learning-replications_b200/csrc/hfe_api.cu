@@ -7,6 +7,7 @@
 
 #include "hfe_kernels.cuh"
 #include "hfe_mma.cuh"
+#include "hfe_forest.cuh"
 #include "hfe_host.cuh"
 
 using namespace hfe;
@@ -164,8 +165,57 @@ int launch_mma(const Model* m, const ScoreParams& P, cudaStream_t stream) {
     return HFE_OK;
 }
 
+// General boosted trees out of shared memory (hfe_forest.cuh).
+template <int W>
+int launch_forest(const Model* m, const ScoreParams& P, cudaStream_t stream) {
+    auto kernel = hfe_forest_kernel<W>;
+    static std::mutex mu;
+    static std::map<int, int> ready;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        if (!ready.count(m->device)) {
+            HFE_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FOREST_SMEM_BYTES));
+            ready[m->device] = 1;
+        }
+    }
+    const long long blocks = (P.n + FOREST_ROWS - 1) / FOREST_ROWS;
+    kernel<<<(unsigned)blocks, FOREST_THREADS, FOREST_SMEM_BYTES, stream>>>(P, m->forest);
+    HFE_CUDA_TRY(cudaGetLastError());
+    return HFE_OK;
+}
+
+int dispatch_score_inner(const Model* m, const ScoreParams& P, cudaStream_t stream);
+
+// Measurement aid (tree_engine 3): the L1 walk with the 8-byte node table pinned in an L2 persisting window for the
+// duration of the launch (the stream's access-policy window is set before and cleared after it).
 int dispatch_score(const Model* m, const ScoreParams& P, cudaStream_t stream) {
+    if (m->tree_mode == 2 && m->tree_engine == 3 && P.nodes) {
+        cudaStreamAttrValue attr{};
+        attr.accessPolicyWindow.base_ptr = const_cast<uint2*>(P.nodes);
+        attr.accessPolicyWindow.num_bytes = std::min<size_t>((size_t)m->n_nodes * sizeof(uint2), 32u << 20);
+        attr.accessPolicyWindow.hitRatio = 1.0f;
+        attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+        HFE_CUDA_TRY(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, 32u << 20));
+        HFE_CUDA_TRY(cudaStreamSetAttribute(stream, cudaStreamAttributeAccessPolicyWindow, &attr));
+        int rc = dispatch_score_inner(m, P, stream);
+        attr.accessPolicyWindow.num_bytes = 0;
+        cudaStreamSetAttribute(stream, cudaStreamAttributeAccessPolicyWindow, &attr);
+        return rc;
+    }
+    return dispatch_score_inner(m, P, stream);
+}
+
+int dispatch_score_inner(const Model* m, const ScoreParams& P, cudaStream_t stream) {
     bool svc = P.slot_svc >= 0;
+    if (!svc && m->tree_mode == 2 && m->forest.n_chunks > 0 && (m->tree_engine == 0 || m->tree_engine == 2)) {
+        const int words = (m->forest.n_pairs + 31) / 32;
+        return words <= 1 ? launch_forest<1>(m, P, stream) : words == 2 ? launch_forest<2>(m, P, stream)
+                                                                       : launch_forest<4>(m, P, stream);
+    }
+    if (m->tree_mode == 2 && m->tree_engine == 2)
+        return fail(HFE_ERR_UNSUPPORTED, "the shared-memory tree walk needs a stack without an SVC member, at most 127 "
+                                         "distinct (feature, threshold) pairs and trees of at most 16 380 nodes");
     if (svc && m->mma.nb > 0 && m->tree_mode != 2 && m->rbf_engine != 1)
         return m->tree_mode == 0 ? launch_mma<0>(m, P, stream) : launch_mma<1>(m, P, stream);
     if (svc && m->rbf_engine == 2)
@@ -348,6 +398,13 @@ int hfe_model_set_rbf_engine(hfe_model* model, int engine) {
     if (!model || !model->impl) return fail(HFE_ERR_INVALID_ARGUMENT, "null model handle");
     if (engine < 0 || engine > 2) return fail(HFE_ERR_INVALID_ARGUMENT, "engine must be 0 (automatic), 1 (SIMT) or 2 (tensor cores)");
     model->impl->rbf_engine = engine;
+    return HFE_OK;
+}
+
+int hfe_model_set_tree_engine(hfe_model* model, int engine) {
+    if (!model || !model->impl) return fail(HFE_ERR_INVALID_ARGUMENT, "null model handle");
+    if (engine < 0 || engine > 3) return fail(HFE_ERR_INVALID_ARGUMENT, "engine must be 0 (automatic), 1 (L1), 2 (shared memory) or 3 (L1 + L2 window)");
+    model->impl->tree_engine = engine;
     return HFE_OK;
 }
 

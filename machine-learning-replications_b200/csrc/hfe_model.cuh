@@ -143,6 +143,21 @@ struct MmaParams {
                                     // column of the B operand (coefficient 0 in the RBF sum) and comes off the tensor core
 };
 
+// General boosted trees walked out of shared memory (hfe_forest.cuh).  Every distinct (feature, threshold) pair of the
+// forest gets an index; a row carries one bit per pair ("x[feature] > threshold"), so a node is 4 bytes -- pair index and
+// in-tree index of the left child -- and a level of the walk is one shared-memory load plus register arithmetic.
+constexpr int FOREST_MAX_PAIRS = 128;          // bits a row carries (4 registers); pair 0 is the constant "false" of leaves
+constexpr int FOREST_CHUNK_NODES = 16384;      // nodes staged per chunk (64 KB); two chunks are resident
+
+struct ForestParams {
+    const unsigned* nodes4;         // per node: pair << 20 | in-tree index of the left child (leaves: pair 0, own index)
+    const int* chunk_tree;          // [n_chunks + 1] first tree of each chunk
+    int n_chunks;
+    int n_pairs;                    // including pair 0
+    int pair_begin[F + 1];          // pairs of feature f: [pair_begin[f], pair_begin[f + 1]), thresholds ascending
+    float pair_thr[FOREST_MAX_PAIRS];
+};
+
 struct HostPipeline;            // hfe_host.cuh: pinned / device slots and the thread pool of large host calls
 
 struct Model {
@@ -156,6 +171,9 @@ struct Model {
     double svc_guard = 0.0;       // assumed |error| of the float32 SVC decision value
     double gbt_guard = 0.0;       // assumed |error| of the float32 boosted raw score
     ScoreParams base{};           // request fields zero; table pointers filled
+    ForestParams forest{};        // n_chunks > 0: general trees can be walked out of shared memory
+    int tree_engine = 0;          // 0 = automatic, 1 = node tables through L1 (__ldg), 2 = shared-memory chunks,
+                                  // 3 = like 1 with the node table pinned in an L2 persisting window (measurement aid)
     MmaParams mma{};              // nb > 0: the RBF sum can run on the tensor cores
     std::vector<unsigned char> mma_img_host;   // B operand image while the model is being built (uploaded by build_model)
     int rbf_engine = 0;           // 0 = automatic (tensor cores when available), 1 = SIMT FFMA2 loop, 2 = tensor cores
@@ -732,6 +750,58 @@ inline int build_gbt(Model* m, const ParsedBlob& pb, uint32_t idx) {
         m->tree_mode = 2;
     }
     int rc;
+    if (m->tree_mode == 2) {
+        // ---- 4-byte nodes + pair table for the shared-memory walk (hfe_forest.cuh) -------------------------------------------
+        std::map<std::pair<int, uint32_t>, int> pair_id;                 // (feature, ordered threshold key) -> index
+        auto key_of = [](uint32_t bits) { return (bits & 0x80000000u) ? ~bits : (bits | 0x80000000u); };   // float order
+        for (int64_t q = 0; q < n_nodes; ++q) {
+            const uint32_t child = nodes[q].y & 0xFFFFFFu;
+            if (child == (uint32_t)q) continue;                          // leaf (self loop)
+            pair_id[{(int)(nodes[q].y >> 24), key_of(nodes[q].x)}] = 0;
+        }
+        bool ok = (int)pair_id.size() + 1 <= FOREST_MAX_PAIRS;
+        ForestParams& Fp = m->forest;
+        std::vector<unsigned> nodes4;
+        std::vector<int> chunk_tree;
+        if (ok) {
+            int next = 1, f_cur = 0;
+            Fp.pair_begin[0] = 1;
+            Fp.pair_thr[0] = INFINITY;
+            for (auto& kv : pair_id) {                                   // sorted by (feature, threshold)
+                while (f_cur < kv.first.first) Fp.pair_begin[++f_cur] = next;
+                const uint32_t key = kv.first.second, bits = (key & 0x80000000u) ? (key & 0x7FFFFFFFu) : ~key;
+                std::memcpy(&Fp.pair_thr[next], &bits, 4);
+                kv.second = next++;
+            }
+            while (f_cur < F) Fp.pair_begin[++f_cur] = next;
+            Fp.n_pairs = next;
+            nodes4.assign((size_t)n_nodes + 8, 0u);
+            chunk_tree.push_back(0);
+            int64_t chunk_start = 0;
+            for (int t = 0; t < n_trees && ok; ++t) {
+                const int base = tree_off[t], cnt = tree_off[t + 1] - tree_off[t];
+                if (cnt + 4 > FOREST_CHUNK_NODES) { ok = false; break; }
+                if ((base + cnt) - (chunk_start & ~(int64_t)3) > FOREST_CHUNK_NODES) {   // copies start 16-byte aligned
+                    chunk_tree.push_back(t);
+                    chunk_start = base;
+                }
+                for (int i = 0; i < cnt; ++i) {
+                    const int64_t q = base + i;
+                    const uint32_t child = nodes[q].y & 0xFFFFFFu;
+                    if (child == (uint32_t)q) nodes4[q] = (uint32_t)i;                 // leaf: pair 0 (never true), own index
+                    else nodes4[q] = ((uint32_t)pair_id[{(int)(nodes[q].y >> 24), key_of(nodes[q].x)}] << 20) | (child - (uint32_t)base);
+                }
+            }
+            chunk_tree.push_back(n_trees);
+        }
+        if (ok) {
+            Fp.n_chunks = (int)chunk_tree.size() - 1;
+            if ((rc = upload(m, nodes4, &Fp.nodes4))) return rc;
+            if ((rc = upload(m, chunk_tree, &Fp.chunk_tree))) return rc;
+        } else {
+            Fp.n_chunks = 0;
+        }
+    }
     if ((rc = upload(m, nodes, &P.nodes))) return rc;
     if ((rc = upload(m, value32, &P.value32))) return rc;
     if ((rc = upload(m, value64, &P.value64))) return rc;

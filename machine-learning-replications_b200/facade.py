@@ -104,6 +104,11 @@ class HFStackB200:
         capi.check(self._lib.hfe_model_get_info(self._handle, C.byref(self.info)))
         return self
 
+    def set_tree_engine(self, engine):
+        """``"auto"`` / ``"l1"`` / ``"smem"`` / ``"l1+l2window"``: how general boosted trees are walked (same results)."""
+        capi.check(self._lib.hfe_model_set_tree_engine(self._handle, {"auto": 0, "l1": 1, "smem": 2, "l1+l2window": 3}[engine]))
+        return self
+
     def close(self):
         if getattr(self, "_handle", None) is not None and self._handle:
             self._lib.hfe_model_destroy(self._handle)
