@@ -97,7 +97,7 @@ int hfe_model_get_info(const hfe_model* model, hfe_model_info* out_info);
 int hfe_model_set_rbf_engine(hfe_model* model, int engine);
 
 /* How general (depth > 1) boosted trees are walked (SK/ensemble/_gradient_boosting.pyx:25-73): 0 = automatic (4-byte nodes
- * streamed through shared memory when the stack has no SVC member and the forest has at most 127 distinct (feature,
+ * streamed through shared memory when the stack has no SVC member and the forest has at most 256 distinct (feature,
  * threshold) pairs, else 8-byte nodes through L1), 1 = always through L1, 2 = shared memory or HFE_ERR_UNSUPPORTED at
  * scoring time, 3 = through L1 with the node table pinned in an L2 persisting window (sets and clears the stream's
  * access-policy window around each launch; kept for measurements).  Same results whichever is used. */

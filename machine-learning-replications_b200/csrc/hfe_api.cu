@@ -166,9 +166,8 @@ int launch_mma(const Model* m, const ScoreParams& P, cudaStream_t stream) {
 }
 
 // General boosted trees out of shared memory (hfe_forest.cuh).
-template <int W>
 int launch_forest(const Model* m, const ScoreParams& P, cudaStream_t stream) {
-    auto kernel = hfe_forest_kernel<W>;
+    auto kernel = hfe_forest_kernel;
     static std::mutex mu;
     static std::map<int, int> ready;
     {
@@ -209,13 +208,11 @@ int dispatch_score(const Model* m, const ScoreParams& P, cudaStream_t stream) {
 int dispatch_score_inner(const Model* m, const ScoreParams& P, cudaStream_t stream) {
     bool svc = P.slot_svc >= 0;
     if (!svc && m->tree_mode == 2 && m->forest.n_chunks > 0 && (m->tree_engine == 0 || m->tree_engine == 2)) {
-        const int words = (m->forest.n_pairs + 31) / 32;
-        return words <= 1 ? launch_forest<1>(m, P, stream) : words == 2 ? launch_forest<2>(m, P, stream)
-                                                                       : launch_forest<4>(m, P, stream);
+        return launch_forest(m, P, stream);
     }
     if (m->tree_mode == 2 && m->tree_engine == 2)
-        return fail(HFE_ERR_UNSUPPORTED, "the shared-memory tree walk needs a stack without an SVC member, at most 127 "
-                                         "distinct (feature, threshold) pairs and trees of at most 16 380 nodes");
+        return fail(HFE_ERR_UNSUPPORTED, "the shared-memory tree walk needs a stack without an SVC member, at most 256 "
+                                         "distinct (feature, threshold) pairs (255 per feature) and trees of at most 16 380 nodes");
     if (svc && m->mma.nb > 0 && m->tree_mode != 2 && m->rbf_engine != 1)
         return m->tree_mode == 0 ? launch_mma<0>(m, P, stream) : launch_mma<1>(m, P, stream);
     if (svc && m->rbf_engine == 2)

@@ -3,11 +3,15 @@
 // The reference walks tree-major over 64-byte Node records (SK/ensemble/_gradient_boosting.pyx:25-73, SK/tree/_tree.pxd:
 // 15-25).  The fused kernel's general-tree walk reads 8-byte nodes through L1 (__ldg): the lanes of a warp sit at different
 // nodes of the same tree, and ncu shows 7.9 sectors per warp-wide load with the L1 tag stage as the bound.  Here
-//   * a row first turns into a bit set: one bit per distinct (feature, threshold) pair of the whole forest, "x[feature] >
-//     threshold" (every schema feature takes a handful of values, so a 2000-tree forest has ~90 pairs);
-//   * a node is 4 bytes: pair index | in-tree index of the left child; one level of the walk is one shared-memory load, a
-//     bit test in registers and an add (leaves point at themselves through pair 0, which is never set, so a fixed-depth
-//     predicated walk needs no exit test);
+//   * per feature the distinct thresholds of the whole forest are sorted (every schema feature takes a handful of values:
+//     a 2000-tree forest has ~90 thresholds in all); a row is turned into 17 bytes, per feature the number of thresholds
+//     below its value, kept in shared memory (one 32-bit word per thread and feature = its four rows);
+//   * a node is 4 bytes: feature | index of its threshold | in-tree index of the left child.  One level of the walk is a
+//     shared-memory load of the node, a byte load of the row's count for that feature, a compare and an add (leaves carry
+//     index 255, which no count exceeds, and point at themselves: a fixed-depth predicated walk needs no exit test).  The
+//     integer pipe runs at half rate on this part, so the step is kept to five integer instructions; address arithmetic
+//     goes to the FMA pipe (IMAD).  A first version that carried the comparisons as a 128-bit set in registers needed
+//     nine and was bound by that pipe at 55-58 M rows/s;
 //   * the node table streams through shared memory in chunks of up to 16 K nodes (64 KB, ~16 trees of the stress forest),
 //     fetched by TMA bulk copies (cp.async.bulk + mbarrier) into two buffers: the whole block walks one chunk while the
 //     copy engine brings the next.  Breadth-first node order puts the first levels of a tree -- the ones all lanes visit --
@@ -20,17 +24,23 @@
 
 namespace hfe {
 
+#ifndef HFE_FOREST_TREES
+#define HFE_FOREST_TREES 4
+#endif
+constexpr int FOREST_TREES = HFE_FOREST_TREES;                         // trees walked side by side by one thread
 constexpr int FOREST_THREADS = 512;
 constexpr int FOREST_ROWS = FOREST_THREADS * ROWS_PER_THREAD;          // 2048 rows per block
 constexpr int FOREST_BUF_BYTES = (FOREST_CHUNK_NODES + 4) * 4;
-constexpr size_t FOREST_SMEM_BYTES = 2 * (size_t)FOREST_BUF_BYTES + 64;
+constexpr int FOREST_BIN_BYTES = F * FOREST_ROWS;                     // one byte per (feature, row of the block)
+constexpr size_t FOREST_SMEM_BYTES = 2 * (size_t)FOREST_BUF_BYTES + FOREST_BIN_BYTES + 64;
 
-template <int W>                                                        // 32-bit words of the per-row bit set
 __global__ void __launch_bounds__(FOREST_THREADS, 1)
 hfe_forest_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ ForestParams Q) {
+    static_assert(FOREST_THREADS * 4 == FOREST_ROWS, "one 32-bit word of counts per thread and feature");
     extern __shared__ __align__(128) unsigned char smem_raw[];
     unsigned* s_buf[2] = {reinterpret_cast<unsigned*>(smem_raw), reinterpret_cast<unsigned*>(smem_raw + FOREST_BUF_BYTES)};
-    unsigned long long* s_bar = reinterpret_cast<unsigned long long*>(smem_raw + 2 * FOREST_BUF_BYTES);
+    unsigned* s_bins = reinterpret_cast<unsigned*>(smem_raw + 2 * FOREST_BUF_BYTES);          // [F][FOREST_THREADS] words
+    unsigned long long* s_bar = reinterpret_cast<unsigned long long*>(smem_raw + 2 * FOREST_BUF_BYTES + FOREST_BIN_BYTES);
     constexpr int R = ROWS_PER_THREAD;
     const int tid = threadIdx.x, lane = tid & 31;
     const long long row0 = ((long long)blockIdx.x * FOREST_THREADS + tid) * R;
@@ -59,16 +69,13 @@ hfe_forest_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__
         if (Q.n_chunks > 1) issue_chunk(1);
     }
 
-    // ---- rows -> bit sets (and the logistic member's dot product) while the first chunks are on their way --------------------
-    unsigned w[R][W];
+    // ---- rows -> per-feature threshold counts (and the logistic member's dot product) while the first chunks are on their way
     double zl[R], raw[R];
     float finite_probe = 0.f;
 #pragma unroll
     for (int r = 0; r < R; ++r) {
         zl[r] = P.lin_intercept;
         raw[r] = P.gbt_init;
-#pragma unroll
-        for (int k = 0; k < W; ++k) w[r][k] = 0u;
     }
     const bool needs_fix = !full || P.perm_col >= 0;
 #pragma unroll
@@ -76,41 +83,25 @@ hfe_forest_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__
         float4 v = load_rows4(P, f, row_ld);
         if (needs_fix) v = fix_rows4(P, f, row0, row_ld, full, v);
         const float xf[R] = {v.x, v.y, v.z, v.w};
+        unsigned cnt[R];
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             if (has_lin) zl[r] = fma((double)xf[r], P.lin_coef[f], zl[r]);
             finite_probe = fmaf(xf[r], 0.f, finite_probe);
+            cnt[r] = 0u;
         }
-        // the pairs of this feature, word by word of the bit set (warp-uniform bounds: a handful of pairs per feature)
-        const int p_lo = Q.pair_begin[f], p_hi = Q.pair_begin[f + 1];
-#pragma unroll
-        for (int k = 0; k < W; ++k) {
-            const int lo = max(p_lo, 32 * k), hi = min(p_hi, 32 * k + 32);
-            unsigned m[R];
-#pragma unroll
-            for (int r = 0; r < R; ++r) m[r] = 0u;
 #pragma unroll 1
-            for (int p = lo; p < hi; ++p) {
-                const float thr = Q.pair_thr[p];
-                const unsigned bit = 1u << (p - 32 * k);
+        for (int k = Q.thr_begin[f]; k < Q.thr_begin[f + 1]; ++k) {         // warp-uniform: a handful of thresholds per feature
+            const float thr = Q.thr[k];
 #pragma unroll
-                for (int r = 0; r < R; ++r) m[r] |= xf[r] > thr ? bit : 0u;
-            }
-#pragma unroll
-            for (int r = 0; r < R; ++r) w[r][k] |= m[r];
+            for (int r = 0; r < R; ++r) cnt[r] += xf[r] > thr ? 1u : 0u;
         }
+        s_bins[f * FOREST_THREADS + tid] = cnt[0] | (cnt[1] << 8) | (cnt[2] << 16) | (cnt[3] << 24);   // own slot: no barrier needed
     }
     const bool nonfinite = !(finite_probe == 0.f);
-    // the bit set as two 64-bit halves held in scalars: a bit test is a select and a funnel shift, never an indexed array
-    unsigned long long b_lo[R], b_hi[R];
-#pragma unroll
-    for (int r = 0; r < R; ++r) {
-        b_lo[r] = (unsigned long long)w[r][0] | (W > 1 ? (unsigned long long)w[r][W > 1 ? 1 : 0] << 32 : 0ull);
-        b_hi[r] = W > 2 ? ((unsigned long long)w[r][W > 2 ? 2 : 0] | ((unsigned long long)w[r][W > 3 ? 3 : 0] << 32)) : 0ull;
-    }
     __syncthreads();                                                      // the barriers are initialised
 
-    // ---- the walk: chunk by chunk, two trees at a time (8 independent chains per thread) ---------------------------------------
+    // ---- the walk: chunk by chunk, FOREST_TREES trees at a time ---------------------------------------
     for (int c = 0; c < Q.n_chunks; ++c) {
         const unsigned* nodes = reinterpret_cast<const unsigned*>(smem_raw + (c & 1) * FOREST_BUF_BYTES);
         {
@@ -131,33 +122,47 @@ hfe_forest_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__
 #pragma unroll
         for (int r = 0; r < R; ++r) acc[r] = 0.f;
         int folded = 0;
-        for (int t = t_begin; t < t_end; t += 2) {
-            const bool two = t + 1 < t_end;
-            const int tb = two ? t + 1 : t;
-            const int off_a = __ldg(P.tree_off + t), off_b = __ldg(P.tree_off + tb);
-            const unsigned* na = nodes + (off_a - origin);
-            const unsigned* nbp = nodes + (off_b - origin);
-            const int depth = max((int)__ldg(P.tree_depth + t), (int)__ldg(P.tree_depth + tb));
-            unsigned ia[R], ib[R];
+        for (int t = t_begin; t < t_end; t += FOREST_TREES) {
+            // FOREST_TREES trees at a time: FOREST_TREES x R independent chains per thread (the walk is bound by the latency of
+            // one level: shared-memory load -> bit test -> add); a short last group repeats its last tree and drops the copy
+            unsigned base[FOREST_TREES];
+            int off[FOREST_TREES], depth = 0;
 #pragma unroll
-            for (int r = 0; r < R; ++r) { ia[r] = 0u; ib[r] = 0u; }
+            for (int k = 0; k < FOREST_TREES; ++k) {
+                const int tk = min(t + k, t_end - 1);
+                off[k] = __ldg(P.tree_off + tk);
+                base[k] = (unsigned)__cvta_generic_to_shared(nodes) + (unsigned)(off[k] - origin) * 4u;
+                depth = max(depth, (int)__ldg(P.tree_depth + tk));
+            }
+            unsigned at[FOREST_TREES][R];                 // byte address of each chain's node
+#pragma unroll
+            for (int k = 0; k < FOREST_TREES; ++k)
+#pragma unroll
+                for (int r = 0; r < R; ++r) at[k][r] = base[k];
+            const unsigned bins0 = (unsigned)__cvta_generic_to_shared(s_bins) + (unsigned)tid * 4u;
             for (int lvl = 0; lvl < depth; ++lvl) {
 #pragma unroll
                 for (int r = 0; r < R; ++r) {
-                    const unsigned da = na[ia[r]], db = nbp[ib[r]];
-                    const unsigned pa = da >> 20, pb = db >> 20;
-                    const unsigned long long sa = (W > 2 && pa >= 64u) ? b_hi[r] : b_lo[r];
-                    const unsigned long long sb = (W > 2 && pb >= 64u) ? b_hi[r] : b_lo[r];
-                    ia[r] = (da & 0xFFFFFu) + ((unsigned)(sa >> (pa & 63u)) & 1u);
-                    ib[r] = (db & 0xFFFFFu) + ((unsigned)(sb >> (pb & 63u)) & 1u);
+#pragma unroll
+                    for (int k = 0; k < FOREST_TREES; ++k) {
+                        unsigned d, c;
+                        asm("ld.shared.u32 %0, [%1];" : "=r"(d) : "r"(at[k][r]));
+                        // node: feature | threshold index | in-tree index of the left child; the row's count for that feature is
+                        // byte r of the thread's word in row `feature` of the table
+                        asm("ld.shared.u8 %0, [%1];" : "=r"(c) : "r"((d >> 24) * (unsigned)(FOREST_THREADS * 4) + (bins0 + r)));
+                        const unsigned step = c > __byte_perm(d, 0u, 0x4442u) ? 4u : 0u;
+                        at[k][r] = (d & 0xFFFFu) * 4u + base[k] + step;
+                    }
                 }
             }
 #pragma unroll
-            for (int r = 0; r < R; ++r) {
-                acc[r] += __ldg(P.value32 + off_a + ia[r]);
-                if (two) acc[r] += __ldg(P.value32 + off_b + ib[r]);
+            for (int k = 0; k < FOREST_TREES; ++k) {
+                const bool live = t + k < t_end;
+#pragma unroll
+                for (int r = 0; r < R; ++r)
+                    if (live) acc[r] += __ldg(P.value32 + off[k] + (int)((at[k][r] - base[k]) >> 2));
             }
-            folded += 2;
+            folded += FOREST_TREES;
             if (folded >= TREE_CHUNK) {                                   // float32 partial sums never span more than 16 trees
 #pragma unroll
                 for (int r = 0; r < R; ++r) { raw[r] += (double)acc[r]; acc[r] = 0.f; }

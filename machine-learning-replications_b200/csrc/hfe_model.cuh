@@ -143,19 +143,21 @@ struct MmaParams {
                                     // column of the B operand (coefficient 0 in the RBF sum) and comes off the tensor core
 };
 
-// General boosted trees walked out of shared memory (hfe_forest.cuh).  Every distinct (feature, threshold) pair of the
-// forest gets an index; a row carries one bit per pair ("x[feature] > threshold"), so a node is 4 bytes -- pair index and
-// in-tree index of the left child -- and a level of the walk is one shared-memory load plus register arithmetic.
-constexpr int FOREST_MAX_PAIRS = 128;          // bits a row carries (4 registers); pair 0 is the constant "false" of leaves
+// General boosted trees walked out of shared memory (hfe_forest.cuh).  Per feature the distinct thresholds of the whole
+// forest are sorted; a row carries, per feature, the number of thresholds below its value (one byte), and a node is 4
+// bytes -- feature, index of its threshold in that feature's list, in-tree index of the left child -- so a level of the
+// walk is two shared-memory loads and a handful of integer instructions.
+constexpr int FOREST_MAX_THR = 256;            // distinct (feature, threshold) pairs of the forest, at most 255 per feature
 constexpr int FOREST_CHUNK_NODES = 16384;      // nodes staged per chunk (64 KB); two chunks are resident
 
 struct ForestParams {
-    const unsigned* nodes4;         // per node: pair << 20 | in-tree index of the left child (leaves: pair 0, own index)
+    const unsigned* nodes4;         // per node: feature << 24 | threshold index << 16 | in-tree index of the left child
+                                    // (leaves: feature 0, index 255 -- never exceeded -- and their own index)
     const int* chunk_tree;          // [n_chunks + 1] first tree of each chunk
     int n_chunks;
-    int n_pairs;                    // including pair 0
-    int pair_begin[F + 1];          // pairs of feature f: [pair_begin[f], pair_begin[f + 1]), thresholds ascending
-    float pair_thr[FOREST_MAX_PAIRS];
+    int n_thr;
+    int thr_begin[F + 1];           // thresholds of feature f: [thr_begin[f], thr_begin[f + 1]), ascending
+    float thr[FOREST_MAX_THR];
 };
 
 struct HostPipeline;            // hfe_host.cuh: pinned / device slots and the thread pool of large host calls
@@ -751,30 +753,33 @@ inline int build_gbt(Model* m, const ParsedBlob& pb, uint32_t idx) {
     }
     int rc;
     if (m->tree_mode == 2) {
-        // ---- 4-byte nodes + pair table for the shared-memory walk (hfe_forest.cuh) -------------------------------------------
-        std::map<std::pair<int, uint32_t>, int> pair_id;                 // (feature, ordered threshold key) -> index
+        // ---- 4-byte nodes + per-feature threshold lists for the shared-memory walk (hfe_forest.cuh) -------------------------
+        std::map<std::pair<int, uint32_t>, int> thr_id;                  // (feature, ordered threshold key) -> index in the feature's list
         auto key_of = [](uint32_t bits) { return (bits & 0x80000000u) ? ~bits : (bits | 0x80000000u); };   // float order
         for (int64_t q = 0; q < n_nodes; ++q) {
             const uint32_t child = nodes[q].y & 0xFFFFFFu;
             if (child == (uint32_t)q) continue;                          // leaf (self loop)
-            pair_id[{(int)(nodes[q].y >> 24), key_of(nodes[q].x)}] = 0;
+            thr_id[{(int)(nodes[q].y >> 24), key_of(nodes[q].x)}] = 0;
         }
-        bool ok = (int)pair_id.size() + 1 <= FOREST_MAX_PAIRS;
+        bool ok = (int)thr_id.size() <= FOREST_MAX_THR;
         ForestParams& Fp = m->forest;
         std::vector<unsigned> nodes4;
         std::vector<int> chunk_tree;
         if (ok) {
-            int next = 1, f_cur = 0;
-            Fp.pair_begin[0] = 1;
-            Fp.pair_thr[0] = INFINITY;
-            for (auto& kv : pair_id) {                                   // sorted by (feature, threshold)
-                while (f_cur < kv.first.first) Fp.pair_begin[++f_cur] = next;
+            int next = 0, f_cur = 0;
+            Fp.thr_begin[0] = 0;
+            for (auto& kv : thr_id) {                                    // sorted by (feature, threshold)
+                while (f_cur < kv.first.first) Fp.thr_begin[++f_cur] = next;
                 const uint32_t key = kv.first.second, bits = (key & 0x80000000u) ? (key & 0x7FFFFFFFu) : ~key;
-                std::memcpy(&Fp.pair_thr[next], &bits, 4);
-                kv.second = next++;
+                std::memcpy(&Fp.thr[next], &bits, 4);
+                kv.second = next - Fp.thr_begin[f_cur];                  // index inside the feature's list
+                ok = ok && kv.second < 255;
+                ++next;
             }
-            while (f_cur < F) Fp.pair_begin[++f_cur] = next;
-            Fp.n_pairs = next;
+            while (f_cur < F) Fp.thr_begin[++f_cur] = next;
+            Fp.n_thr = next;
+        }
+        if (ok) {
             nodes4.assign((size_t)n_nodes + 8, 0u);
             chunk_tree.push_back(0);
             int64_t chunk_start = 0;
@@ -788,8 +793,12 @@ inline int build_gbt(Model* m, const ParsedBlob& pb, uint32_t idx) {
                 for (int i = 0; i < cnt; ++i) {
                     const int64_t q = base + i;
                     const uint32_t child = nodes[q].y & 0xFFFFFFu;
-                    if (child == (uint32_t)q) nodes4[q] = (uint32_t)i;                 // leaf: pair 0 (never true), own index
-                    else nodes4[q] = ((uint32_t)pair_id[{(int)(nodes[q].y >> 24), key_of(nodes[q].x)}] << 20) | (child - (uint32_t)base);
+                    if (child == (uint32_t)q) {
+                        nodes4[q] = (255u << 16) | (uint32_t)i;                           // leaf: the test never holds
+                    } else {
+                        const uint32_t f = nodes[q].y >> 24;
+                        nodes4[q] = (f << 24) | ((uint32_t)thr_id[{(int)f, key_of(nodes[q].x)}] << 16) | (child - (uint32_t)base);
+                    }
                 }
             }
             chunk_tree.push_back(n_trees);
