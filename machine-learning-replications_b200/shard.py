@@ -28,12 +28,60 @@ def dist_env():
             int(os.environ.get("WORLD_SIZE", 1)))
 
 
-def init_process_group(backend=None):
-    """Join the torchrun rendezvous (MASTER_ADDR/MASTER_PORT from the environment).  Returns (rank, local_rank, world)."""
+def _parse_cpulist(text):
+    cpus = set()
+    for part in text.strip().split(","):
+        if not part:
+            continue
+        lo, _, hi = part.partition("-")
+        cpus.update(range(int(lo), int(hi or lo) + 1))
+    return cpus
+
+
+def rank_cpus(local_rank: int, local_world: int, allowed=None, gpu_local_cpus=None):
+    """CPU set for this rank's host threads (the chunk pipeline of ``hfe_predict_host`` narrows rows on host threads and
+    copies out of pinned memory, so eight ranks must not all sit on the same cores): the CPUs local to the rank's GPU
+    (its PCIe root / NUMA node, from sysfs) intersected with what the process may use; ranks that share such a set split
+    it evenly.  Pure function of its arguments (tested on CPU)."""
+    allowed = sorted(allowed if allowed is not None else os.sched_getaffinity(0))
+    pool = sorted(set(allowed) & set(gpu_local_cpus)) if gpu_local_cpus else allowed
+    if not pool:
+        pool = allowed
+    per = max(len(pool) // max(local_world, 1), 1)
+    start = (local_rank * per) % len(pool)
+    mine = pool[start:start + per]
+    return set(mine) if mine else set(pool)
+
+
+def bind_rank_to_gpu_cpus(local_rank: int, local_world: int):
+    """Set this process's CPU affinity with ``rank_cpus``; returns the set (or None where sysfs / affinity calls are not
+    available).  Pinned buffers allocated afterwards are first touched from these cores."""
+    try:
+        import torch
+        local = None
+        if torch.cuda.is_available():
+            bus = torch.cuda.get_device_properties(local_rank).pci_bus_id
+            dom = getattr(torch.cuda.get_device_properties(local_rank), "pci_domain_id", 0)
+            dev = getattr(torch.cuda.get_device_properties(local_rank), "pci_device_id", 0)
+            path = f"/sys/bus/pci/devices/{dom:04x}:{bus:02x}:{dev:02x}.0/local_cpulist"
+            if os.path.exists(path):
+                local = _parse_cpulist(open(path).read())
+        cpus = rank_cpus(local_rank, local_world, gpu_local_cpus=local)
+        os.sched_setaffinity(0, cpus)
+        return cpus
+    except Exception:
+        return None
+
+
+def init_process_group(backend=None, bind_cpus=True):
+    """Join the torchrun rendezvous (MASTER_ADDR/MASTER_PORT from the environment).  Returns (rank, local_rank, world).
+    With more than one rank each process is bound to its share of the CPUs local to its GPU (``bind_rank_to_gpu_cpus``)."""
     import torch
     import torch.distributed as dist
 
     rank, local_rank, world = dist_env()
+    if world > 1 and bind_cpus:
+        bind_rank_to_gpu_cpus(local_rank, int(os.environ.get("LOCAL_WORLD_SIZE", world)))
     if world > 1 and not dist.is_initialized():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         if backend is None:

@@ -25,6 +25,20 @@ def test_shard_ranges_partition_rows(pkg):
         sr(10, 2, 2)
 
 
+def test_rank_cpu_sets_partition_the_local_cores(pkg):
+    rc = pkg.shard.rank_cpus
+    allowed = set(range(32))
+    sets = [rc(r, 8, allowed=allowed) for r in range(8)]
+    assert all(len(s) == 4 for s in sets) and set().union(*sets) == allowed          # one NUMA node: split evenly
+    assert sum(len(s) for s in sets) == 32
+    near = set(range(16, 32))
+    sets = [rc(r, 4, allowed=allowed, gpu_local_cpus=near) for r in range(4)]
+    assert set().union(*sets) == near and all(len(s) == 4 for s in sets)             # only the GPU's own cores
+    assert rc(0, 1, allowed={3, 5}) == {3, 5}
+    assert rc(5, 8, allowed={0, 1}) <= {0, 1} and rc(5, 8, allowed={0, 1})            # more ranks than cores: still a core
+    assert pkg.shard._parse_cpulist("0-3,8,10-11\n") == {0, 1, 2, 3, 8, 10, 11}
+
+
 def _worker(rank, world, port, n_total, tmp):
     sys.path.insert(0, ROOT)
     import importlib
