@@ -137,6 +137,21 @@ int hfe_score(const hfe_model* model, const float* x, int64_t n, int64_t ld, int
               const int32_t* perm_idx, float* out_n2, uint8_t* labels, double* decision, double* meta,
               const uint8_t* y, unsigned long long* score, uint32_t* status, void* stream);
 
+/* Permutation importance, one column (SK/inspection/_permutation_importance.py:31-76): for each selected index vector
+ * perm_idx + sel[k] * perm_stride (int32 row indices, length n) the matrix is scored with column perm_col read through it
+ * and scores[k] += #{labels == y} -- the hfe_score passes of that column enqueued back to back without returning to the
+ * caller in between (perm_col < 0: the baseline pass, sel only counts).  flags[k] (may be NULL) receives that pass's
+ * status[0] error bits; `status` itself is reused by every pass.  sel is a HOST array, everything else device memory. */
+int hfe_score_permuted(const hfe_model* model, const float* x, int64_t n, int64_t ld, int32_t perm_col,
+                       const int32_t* perm_idx, int64_t perm_stride, int32_t n_sel, const int32_t* sel,
+                       const uint8_t* y, unsigned long long* scores, uint32_t* flags, uint32_t* status, void* stream);
+
+/* The index vectors scikit-learn's permutation_importance uses for one column (same file, lines 66-74, 278): a
+ * RandomState(seed) -- numpy's legacy MT19937 stream -- shuffles one index vector n_repeats times in a row and applies it
+ * each time to the already permuted column; out[r*n + i] is the row whose value lands in row i at repeat r.  Host
+ * memory only, no device work; bit-for-bit numpy's RandomState.shuffle. */
+int hfe_perm_indices(uint32_t seed, int64_t n, int32_t n_repeats, int32_t* out);
+
 /* GradientBoostingClassifier.apply (SK/ensemble/_gb.py:1104-1135; SK/tree/_tree.pyx:954-996): scikit-learn node id of
  * the leaf each row reaches in each tree, leaves[i*n_trees + t], uint16 (parity mode; not on the timed path). */
 int hfe_apply(const hfe_model* model, const float* x, int64_t n, int64_t ld, uint16_t* leaves, void* stream);

@@ -474,6 +474,81 @@ int hfe_score_f64(const hfe_model* model, const float* x, int64_t n, int64_t ld,
                         stream, true);
 }
 
+int hfe_score_permuted(const hfe_model* model, const float* x, int64_t n, int64_t ld, int32_t perm_col,
+                       const int32_t* perm_idx, int64_t perm_stride, int32_t n_sel, const int32_t* sel,
+                       const uint8_t* y, unsigned long long* scores, uint32_t* flags, uint32_t* status, void* stream) {
+    if (n_sel < 0 || (n_sel > 0 && (!sel || !scores || !y))) return fail(HFE_ERR_INVALID_ARGUMENT, "bad permuted-pass selection");
+    if (perm_col >= 0 && perm_stride < n) return fail(HFE_ERR_INVALID_ARGUMENT, "index vectors overlap");
+    for (int32_t k = 0; k < n_sel; ++k) {
+        if (sel[k] < 0) return fail(HFE_ERR_INVALID_ARGUMENT, "negative index-vector number");
+        int rc = score_common(model, x, n, ld, perm_col, perm_col >= 0 ? perm_idx + (int64_t)sel[k] * perm_stride : nullptr,
+                              nullptr, nullptr, nullptr, nullptr, nullptr, y, scores + k, status, stream, false);
+        if (rc) return rc;
+        if (flags)      // the status array is reused by the next pass: keep this pass's error bits
+            HFE_CUDA_TRY(cudaMemcpyAsync(flags + k, status, sizeof(uint32_t), cudaMemcpyDeviceToDevice,
+                                         static_cast<cudaStream_t>(stream)));
+    }
+    return HFE_OK;
+}
+
+namespace {
+// numpy's legacy generator (RandomState): MT19937 seeded by init_genrand, 32-bit draws
+struct Mt19937 {
+    uint32_t mt[624];
+    int pos = 624;
+    explicit Mt19937(uint32_t seed) {
+        mt[0] = seed;
+        for (int i = 1; i < 624; ++i) mt[i] = 1812433253u * (mt[i - 1] ^ (mt[i - 1] >> 30)) + (uint32_t)i;
+    }
+    void refill() {
+        for (int k = 0; k < 624; ++k) {
+            const uint32_t yv = (mt[k] & 0x80000000u) | (mt[(k + 1) % 624] & 0x7FFFFFFFu);
+            mt[k] = mt[(k + 397) % 624] ^ (yv >> 1) ^ ((yv & 1u) ? 0x9908B0DFu : 0u);
+        }
+        pos = 0;
+    }
+    uint32_t next() {
+        if (pos >= 624) refill();
+        uint32_t v = mt[pos++];
+        v ^= v >> 11;
+        v ^= (v << 7) & 0x9D2C5680u;
+        v ^= (v << 15) & 0xEFC60000u;
+        v ^= v >> 18;
+        return v;
+    }
+};
+}  // namespace
+
+int hfe_perm_indices(uint32_t seed, int64_t n, int32_t n_repeats, int32_t* out) {
+    if (n < 0 || n > 0x7FFFFFFF || n_repeats < 0 || (!out && n > 0 && n_repeats > 0))
+        return fail(HFE_ERR_INVALID_ARGUMENT, "bad permutation request");
+    try {
+        Mt19937 rng(seed);
+        std::vector<int32_t> idx((size_t)n);
+        for (int64_t i = 0; i < n; ++i) idx[(size_t)i] = (int32_t)i;
+        for (int32_t r = 0; r < n_repeats; ++r) {
+            // RandomState.shuffle: for i = n-1 .. 1: j = random_interval(i) (masked rejection on 32-bit draws); swap
+            for (int64_t i = n - 1; i >= 1; --i) {
+                uint32_t mask = (uint32_t)i;
+                mask |= mask >> 1; mask |= mask >> 2; mask |= mask >> 4; mask |= mask >> 8; mask |= mask >> 16;
+                uint32_t j;
+                while ((j = rng.next() & mask) > (uint32_t)i) {}
+                std::swap(idx[(size_t)i], idx[j]);
+            }
+            // the shuffled vector is applied to the already permuted column: effective source index e_r = e_{r-1}[idx]
+            int32_t* cur = out + (size_t)r * (size_t)n;
+            if (r == 0) std::memcpy(cur, idx.data(), (size_t)n * sizeof(int32_t));
+            else {
+                const int32_t* prev = cur - n;
+                for (int64_t i = 0; i < n; ++i) cur[i] = prev[idx[(size_t)i]];
+            }
+        }
+    } catch (const std::exception& e) {
+        return fail(HFE_ERR_INVALID_ARGUMENT, std::string("out of host memory: ") + e.what());
+    }
+    return HFE_OK;
+}
+
 int hfe_apply(const hfe_model* model, const float* x, int64_t n, int64_t ld, uint16_t* leaves, void* stream) {
     int rc = check_matrix(model, x, n, ld);
     if (rc) return rc;

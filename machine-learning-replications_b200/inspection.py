@@ -6,7 +6,7 @@ Same procedure as ``sklearn.inspection.permutation_importance`` (SK/inspection/_
 applies it each time to the already permuted column, and scores the matrix.  Here the ``n_repeats`` index vectors are made
 once on the host (so they are exactly scikit-learn's), uploaded as int32, and each (column, repeat) pass is one launch
 of the fused kernel with ``perm_col`` / ``perm_idx`` -- the shuffled matrix is never materialised -- and an on-device
-count of ``label == y``.  With several ranks the 17 x n_repeats passes are dealt round-robin and the counts are summed
+count of ``label == y``.  With several ranks the 17 x n_repeats passes are dealt in contiguous blocks and the counts are summed
 with one all-reduce of 86 integers; every rank holds the full matrix (1 M rows = 68 MB).
 """
 from __future__ import annotations
@@ -24,7 +24,8 @@ class ImportanceResult(dict):
 def shuffled_indices(n_samples: int, n_repeats: int, random_seed: int) -> np.ndarray:
     """Row r = where the permuted column's values come from at repeat r.  scikit-learn keeps shuffling one index vector
     and applies it to the *already permuted* column (``X_permuted[:, j] = X_permuted[shuffling_idx, j]``,
-    SK/inspection/_permutation_importance.py:66-74), so the effective source index composes: e_r = e_{r-1}[s_r]."""
+    SK/inspection/_permutation_importance.py:66-74), so the effective source index composes: e_r = e_{r-1}[s_r].
+    numpy restatement (the checker of ``native_shuffled_indices``)."""
     rng = np.random.RandomState(random_seed)
     idx = np.arange(n_samples)
     eff = np.arange(n_samples)
@@ -33,6 +34,16 @@ def shuffled_indices(n_samples: int, n_repeats: int, random_seed: int) -> np.nda
         rng.shuffle(idx)
         eff = eff[idx]
         out[r] = eff
+    return out
+
+
+def native_shuffled_indices(n_samples: int, n_repeats: int, random_seed: int) -> np.ndarray:
+    """The same vectors from ``hfe_perm_indices`` (numpy's legacy MT19937 stream and masked-rejection shuffle restated in
+    C++, bit for bit): no Python-level arrays of 8-byte indices, half the time of five ``RandomState.shuffle`` calls."""
+    import ctypes as C
+    out = np.empty((n_repeats, n_samples), dtype=np.int32)
+    capi.check(capi.load_library().hfe_perm_indices(int(random_seed) & 0xFFFFFFFF, n_samples, n_repeats,
+                                                    out.ctypes.data_as(C.c_void_p)))
     return out
 
 
@@ -73,7 +84,7 @@ def permutation_importance(clf, x, y, n_repeats: int = 5, random_state=None, ran
     rs = random_state if isinstance(random_state, np.random.RandomState) else np.random.RandomState(random_state)
     random_seed = rs.randint(np.iinfo(np.int32).max + 1)         # SK/inspection/_permutation_importance.py:278
     if shuffle == "sklearn":
-        perms = torch.from_numpy(shuffled_indices(n, n_repeats, random_seed)).to(dev)
+        perms = torch.from_numpy(native_shuffled_indices(n, n_repeats, random_seed)).to(dev)
     else:
         perms = shuffled_indices_device(n, n_repeats, random_seed, dev)
     n_feat = clf.n_features_in_
@@ -81,12 +92,21 @@ def permutation_importance(clf, x, y, n_repeats: int = 5, random_state=None, ran
     status = clf.new_status()
     jobs = [(-1, 0)] + [(c, r) for c in range(n_feat) for r in range(n_repeats)]
     flags = torch.zeros(len(jobs), dtype=torch.int32, device=dev)      # status[0] of every pass (one array is reused)
-    for k, (col, rep) in enumerate(jobs):
-        if k % world != rank:
-            continue
-        clf.score_device(x, n=n, perm_col=col, perm_idx=perms[rep] if col >= 0 else None, y=y_dev,
-                         score=counts[k:k + 1], status=status)
-        flags[k:k + 1].copy_(status[:1])
+    # this rank's passes, column by column: one C call enqueues all repeats of a column back to back
+    import ctypes as C
+    lib, stream = capi.load_library(), torch.cuda.current_stream(dev).cuda_stream
+    mine = list(range(len(jobs) * rank // world, len(jobs) * (rank + 1) // world))      # a contiguous block of passes per rank
+    with torch.cuda.device(dev):
+        at = 0
+        while at < len(mine):
+            col = jobs[mine[at]][0]
+            run = [k for k in mine[at:] if jobs[k][0] == col]
+            sel = (C.c_int32 * len(run))(*[jobs[k][1] for k in run])
+            capi.check(lib.hfe_score_permuted(clf._handle, x.data_ptr(), n, x.stride(0), col,
+                                              perms.data_ptr() if col >= 0 else None, perms.stride(0), len(run), sel,
+                                              y_dev.data_ptr(), counts[run[0]:].data_ptr(), flags[run[0]:].data_ptr(),
+                                              status.data_ptr(), stream))
+            at += len(run)
     flags_host = flags.cpu().numpy()
     if (flags_host & capi.ROW_NONFINITE).any():
         raise ValueError("Input X contains NaN or infinity.")          # what scikit-learn's scorer raises
