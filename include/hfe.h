@@ -28,7 +28,8 @@
  *           re-evaluation (then the rows beyond the capacity keep their float32-path result: rerun the batch through
  *           hfe_predict_proba_f64, as the Python facade does);
  *       [1] number of rows that were re-evaluated in float64 ("guard bands");
- *       [2] work-list length, [3] reserved, [4..] the work list itself (row indices).  The work list is scratch
+ *       [2] work-list length, [3] reserved (the checked build counts completed appends there), [4..] the work list
+ *           itself (row indices).  The work list is scratch
  *           memory of the call: the fused kernel appends the rows whose result hinges on a branch (coupling-solver
  *           exit test, label sign), a second small kernel re-evaluates exactly those rows in float64.
  *     Two calls that overlap on the device must not share a status array.  n must be < 2^32 rows per call.
@@ -81,6 +82,15 @@ typedef struct hfe_model_info {
     uint64_t device_bytes;         /* bytes of device memory the handle owns */
     int32_t rbf_engine;            /* what scores the RBF sum: 0 no SVC member, 1 SIMT FFMA2 loop, 2 tensor cores (tcgen05) */
     int32_t rbf_exp_per_row;       /* exponentials the active engine evaluates per row (tensor cores: padded column count) */
+    /* the creation-time guard probe (hfe_model_create): the band in use, and what the probe batch showed */
+    double  svc_observed_err;      /* max |fast - float64| of the SVC decision value over the probe rows the fast engines
+                                    * (SIMT and, where usable, tensor cores) did not hand to the float64 re-evaluation */
+    double  label_guard;           /* |combiner decision value| below this => the row is re-evaluated in float64 */
+    double  label_observed_err;    /* max |fast - float64| of the combiner's decision value over the same rows */
+    double  svc_observed_by_engine[2];   /* the same per engine: [0] SIMT loop, [1] tensor cores (0 where not usable) */
+    int32_t probe_rows;            /* rows in the probe batch (0: no SVC member, or hfe_model_plan) */
+    int32_t guard_widened;         /* bit 0: svc_guard was below 8 x svc_observed_err and was raised to it; bit 1: the same
+                                    * for label_guard */
 } hfe_model_info;
 
 /* Replaces pickle.load('./hf_predict_model.pkl') (predict_hf.py:33-34): validates the flat blob written by
@@ -89,6 +99,13 @@ typedef struct hfe_model_info {
 int hfe_model_create(const void* blob, size_t blob_bytes, int device, hfe_model** out_model);
 void hfe_model_destroy(hfe_model* model);
 int hfe_model_get_info(const hfe_model* model, hfe_model_info* out_info);
+/* Re-runs the guard probe hfe_model_create ends with.  The bands are first derived from the model's coefficients by a formula
+ * (DESIGN.md "error budget"), multiplied by `formula_scale` (1 at creation); then 65 536 probe rows -- the support vectors in
+ * raw units and crossovers of pairs of them -- go through every fast engine and through the all-float64 kernel, and a band
+ * below 8 x the observed |fast - float64| is raised to that.  formula_scale > 1 buys wider bands (more rows re-evaluated in
+ * float64); < 1 exists for the test that shows the probe catching a band that is too narrow.  Allocates and synchronises;
+ * not to be called while other threads score with the handle. */
+int hfe_model_calibrate_guards(hfe_model* model, double formula_scale);
 /* Which engine evaluates the RBF sum of the SVC member (svm.cpp:461-515, 2821-2904): 0 = automatic (the tensor-core kernel
  * when the model fits it: at most ~460 support vectors -- its operand tables share one SM's shared memory -- and no
  * general tree tables), 1 = the SIMT FFMA2 loop, 2 = the

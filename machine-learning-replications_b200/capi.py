@@ -20,7 +20,7 @@ NOALLOC_MAX_ROWS = 1 << 26
 METRIC_BINS = 65536
 
 EXPORTS = [
-    "hfe_abi_version", "hfe_last_error_string", "hfe_model_create", "hfe_model_destroy", "hfe_model_get_info", "hfe_model_plan", "hfe_model_set_rbf_engine", "hfe_model_set_tree_engine",
+    "hfe_abi_version", "hfe_last_error_string", "hfe_model_calibrate_guards", "hfe_model_create", "hfe_model_destroy", "hfe_model_get_info", "hfe_model_plan", "hfe_model_set_rbf_engine", "hfe_model_set_tree_engine",
     "hfe_predict_proba", "hfe_predict", "hfe_score", "hfe_score_permuted", "hfe_perm_indices", "hfe_apply", "hfe_predict_proba_f64", "hfe_score_f64", "hfe_synth_rows",
     "hfe_ingest_rowmajor_f64", "hfe_ingest_rowmajor_f32", "hfe_ingest_rowmajor_i64", "hfe_ingest_rowmajor_u8", "hfe_knn1_impute", "hfe_predict_host", "hfe_predict_proba_noalloc", "hfe_binary_metrics",
 ]
@@ -39,6 +39,8 @@ class ModelInfo(C.Structure):
         ("max_tree_depth", C.c_int32), ("tree_mode", C.c_int32), ("n_merged_splits", C.c_int32),
         ("device", C.c_int32), ("rbf_fma_per_row", C.c_int32), ("svc_guard", C.c_double), ("device_bytes", C.c_uint64),
         ("rbf_engine", C.c_int32), ("rbf_exp_per_row", C.c_int32),
+        ("svc_observed_err", C.c_double), ("label_guard", C.c_double), ("label_observed_err", C.c_double),
+        ("svc_observed_by_engine", C.c_double * 2), ("probe_rows", C.c_int32), ("guard_widened", C.c_int32),
     ]
 
 
@@ -62,6 +64,7 @@ def load_library(path: str = LIB_PATH):
     lib.hfe_model_destroy.argtypes = [vp]
     lib.hfe_model_destroy.restype = None
     lib.hfe_model_get_info.argtypes = [vp, C.POINTER(ModelInfo)]
+    lib.hfe_model_calibrate_guards.argtypes = [vp, C.c_double]
     lib.hfe_model_set_rbf_engine.argtypes = [vp, C.c_int]
     lib.hfe_model_set_tree_engine.argtypes = [vp, C.c_int]
     lib.hfe_model_plan.argtypes = [vp, C.c_size_t, C.POINTER(ModelInfo), C.POINTER(C.c_int32)]

@@ -241,7 +241,8 @@ int dispatch_score_inner(const Model* m, const ScoreParams& P, cudaStream_t stre
 
 int score_common(const hfe_model* model, const float* x, int64_t n, int64_t ld, int32_t perm_col,
                  const int32_t* perm_idx, float* out, double* out64, uint8_t* labels, double* decision, double* meta,
-                 const uint8_t* y, unsigned long long* score, uint32_t* status, void* stream, bool all_f64) {
+                 const uint8_t* y, unsigned long long* score, uint32_t* status, void* stream, bool all_f64,
+                 double* svc_dec = nullptr) {
     int rc = check_matrix(model, x, n, ld);
     if (rc) return rc;
     if (!status) return fail(HFE_ERR_INVALID_ARGUMENT, "null status array");
@@ -267,6 +268,7 @@ int score_common(const hfe_model* model, const float* x, int64_t n, int64_t ld, 
     P.labels = labels;
     P.decision = decision;
     P.meta = meta;
+    P.svc_dec = svc_dec;
     P.y = y;
     P.score = score;
     P.status = status;
@@ -280,8 +282,119 @@ int score_common(const hfe_model* model, const float* x, int64_t n, int64_t ld, 
     }
     rc = dispatch_score(m, P, s);
     if (rc) return rc;
+    P.svc_dec = nullptr;                // the probe wants the fast pass's decision values, not the re-evaluated ones
     hfe_fixup_kernel<<<(unsigned)sms, BLOCK_THREADS, 0, s>>>(P);       // re-evaluates the rows the fused kernel put on the work list
     HFE_CUDA_TRY(cudaGetLastError());
+    return HFE_OK;
+}
+
+// ---- creation-time guard probe ---------------------------------------------------------------------------------------------
+// The guard bands are derived from a formula (build_svc: ~20 sigma of the error measured while the kernels were written).
+// This turns the formula into a checked contract: a fixed probe batch -- the model's own support vectors mapped back to
+// raw units, and crossovers between pairs of them, so the rows sit where the RBF terms are largest and stay on the integer
+// lattice the cohort lives on -- is scored by every fast engine the model can use and by the all-float64 kernel; the largest
+// |fast - float64| of the SVC decision value and of the combiner's decision value over the rows the fast pass did NOT hand to
+// the fix-up is kept in the handle (hfe_model_info), and a band narrower than 8 x what was observed is widened to that.
+constexpr int PROBE_ROWS = 65536;
+
+int probe_guards(hfe_model* h) {
+    Model* m = h->impl;
+    m->svc_observed_err = m->label_observed_err = 0.0;
+    m->svc_observed_by_engine[0] = m->svc_observed_by_engine[1] = 0.0;
+    m->probe_rows = 0;
+    m->guard_widened = 0;
+    m->svc_guard = m->svc_guard_formula * m->guard_scale;
+    derive_guards(m);
+    const ScoreParams& B = m->base;
+    if (B.slot_svc < 0 || B.n_sv <= 0) return HFE_OK;
+    HFE_CUDA_TRY(cudaSetDevice(m->device));
+    const int64_t n = PROBE_ROWS, ld = PROBE_ROWS;
+    std::vector<double> sv((size_t)B.n_sv * F);
+    HFE_CUDA_TRY(cudaMemcpy(sv.data(), B.sv64, sv.size() * sizeof(double), cudaMemcpyDeviceToHost));
+    std::vector<float> hx((size_t)F * ld);
+    for (int64_t i = 0; i < n; ++i) {
+        uint64_t z = (uint64_t)i * 0x9E3779B97F4A7C15ull + 0xD1B54A32D192ED03ull;        // splitmix64 of the row number
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+        z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+        z ^= z >> 31;
+        const int j = (int)(i % B.n_sv), j2 = (int)((z >> 1) % (uint64_t)B.n_sv);
+        const unsigned cross = i < B.n_sv ? 0u : (unsigned)((z >> 20) & (z >> 40));         // each feature with probability 1/4
+        for (int d = 0; d < F; ++d) {
+            const double s = sv[(size_t)(((cross >> d) & 1u) ? j2 : j) * F + d];
+            double v = B.mean[d] + B.scale[d] * s;
+            const double r = std::nearbyint(v);
+            if (std::fabs(v - r) <= 1e-6 * std::max(1.0, std::fabs(v))) v = r;
+            hx[(size_t)m->col_of[d] * ld + i] = (float)v;
+        }
+    }
+    const size_t x_bytes = hx.size() * sizeof(float), col_bytes = (size_t)n * sizeof(double);
+    const size_t status_bytes = HFE_STATUS_WORDS * sizeof(uint32_t);
+    unsigned char* arena = nullptr;
+    HFE_CUDA_TRY(cudaMalloc(&arena, x_bytes + 4 * col_bytes + status_bytes));
+    float* dx = reinterpret_cast<float*>(arena);
+    double* d_dec[2] = {reinterpret_cast<double*>(arena + x_bytes), reinterpret_cast<double*>(arena + x_bytes + col_bytes)};
+    double* d_svc[2] = {reinterpret_cast<double*>(arena + x_bytes + 2 * col_bytes),
+                        reinterpret_cast<double*>(arena + x_bytes + 3 * col_bytes)};
+    uint32_t* d_status = reinterpret_cast<uint32_t*>(arena + x_bytes + 4 * col_bytes);
+    cudaStream_t s = cudaStreamPerThread;
+    std::vector<double> dec64(n), svc64(n), dec(n), svc(n);
+    std::vector<uint32_t> status(HFE_STATUS_WORDS);
+    std::vector<unsigned char> flagged(n);
+    const int engine_before = m->rbf_engine;
+    int rc = HFE_OK;
+    auto run = [&]() -> int {
+        HFE_CUDA_TRY(cudaMemcpyAsync(dx, hx.data(), x_bytes, cudaMemcpyHostToDevice, s));
+        int r = score_common(h, dx, n, ld, -1, nullptr, nullptr, nullptr, nullptr, d_dec[1], nullptr, nullptr, nullptr,
+                             d_status, s, true, d_svc[1]);
+        if (r) return r;
+        HFE_CUDA_TRY(cudaMemcpyAsync(dec64.data(), d_dec[1], col_bytes, cudaMemcpyDeviceToHost, s));
+        HFE_CUDA_TRY(cudaMemcpyAsync(svc64.data(), d_svc[1], col_bytes, cudaMemcpyDeviceToHost, s));
+        double e_f = 0.0, e_z = 0.0;
+        bool probed = false;
+        for (int engine = 1; engine <= 2; ++engine) {
+            if (engine == 2 && !(m->mma.nb > 0 && m->tree_mode != 2)) continue;
+            m->rbf_engine = engine;
+            r = score_common(h, dx, n, ld, -1, nullptr, nullptr, nullptr, nullptr, d_dec[0], nullptr, nullptr, nullptr,
+                             d_status, s, false, d_svc[0]);
+            if (r == HFE_ERR_UNSUPPORTED) continue;         // this engine cannot score the model (table too large): nothing to check
+            if (r) return r;
+            HFE_CUDA_TRY(cudaMemcpyAsync(dec.data(), d_dec[0], col_bytes, cudaMemcpyDeviceToHost, s));
+            HFE_CUDA_TRY(cudaMemcpyAsync(svc.data(), d_svc[0], col_bytes, cudaMemcpyDeviceToHost, s));
+            HFE_CUDA_TRY(cudaMemcpyAsync(status.data(), d_status, status_bytes, cudaMemcpyDeviceToHost, s));
+            HFE_CUDA_TRY(cudaStreamSynchronize(s));
+            probed = true;
+            std::fill(flagged.begin(), flagged.end(), 0);
+            const uint32_t len = std::min<uint32_t>(status[HFE_STATUS_LIST_LEN], HFE_WORKLIST_CAPACITY);
+            for (uint32_t k = 0; k < len; ++k) flagged[status[HFE_STATUS_HEADER_WORDS + k]] = 1;
+            for (int64_t i = 0; i < n; ++i) {
+                if (flagged[i]) continue;
+                const double df = std::fabs(svc[i] - svc64[i]), dz = std::fabs(dec[i] - dec64[i]);
+                if (df == df) {
+                    e_f = std::max(e_f, df);
+                    m->svc_observed_by_engine[engine - 1] = std::max(m->svc_observed_by_engine[engine - 1], df);
+                }
+                if (dz == dz) e_z = std::max(e_z, dz);
+            }
+        }
+        m->svc_observed_err = e_f;
+        m->label_observed_err = e_z;
+        m->probe_rows = probed ? (int)n : 0;
+        return HFE_OK;
+    };
+    rc = run();
+    m->rbf_engine = engine_before;
+    cudaStreamSynchronize(s);
+    cudaFree(arena);
+    if (rc) return rc;
+    if (m->svc_guard < 8.0 * m->svc_observed_err) {
+        m->svc_guard = 8.0 * m->svc_observed_err;
+        m->guard_widened |= 1;
+        derive_guards(m);
+    }
+    if (m->base.label_guard < 8.0 * m->label_observed_err) {
+        m->base.label_guard = 8.0 * m->label_observed_err;
+        m->guard_widened |= 2;
+    }
     return HFE_OK;
 }
 
@@ -310,7 +423,7 @@ int ingest_common(const T* x_rowmajor, int64_t n, int32_t n_features, float* x, 
 
 extern "C" {
 
-int hfe_abi_version(void) { return 1; }
+int hfe_abi_version(void) { return 2; }
 
 const char* hfe_last_error_string(void) { return g_last_error.c_str(); }
 
@@ -359,8 +472,20 @@ int hfe_model_create(const void* blob, size_t blob_bytes, int device, hfe_model*
         delete impl;
         return fail(HFE_ERR_INVALID_ARGUMENT, "out of host memory");
     }
+    rc = probe_guards(h);                   // the guard bands as a checked contract (see probe_guards)
+    if (rc) {
+        hfe_model_destroy(h);
+        return rc;
+    }
     *out_model = h;
     return HFE_OK;
+}
+
+int hfe_model_calibrate_guards(hfe_model* model, double formula_scale) {
+    if (!model) return fail(HFE_ERR_INVALID_ARGUMENT, "null model");
+    if (!(formula_scale > 0.0) || !(formula_scale <= 1e12)) return fail(HFE_ERR_INVALID_ARGUMENT, "formula_scale must be positive and finite");
+    model->impl->guard_scale = formula_scale;
+    return probe_guards(model);
 }
 
 void hfe_model_destroy(hfe_model* model) {
@@ -435,6 +560,13 @@ static void fill_info(const Model* m, hfe_model_info* info) {
                             : m->base.sv_quads > 0 ? 4 * (m->base.sv_quads * SV_PREFIX + m->sv_steps * SV_LEAF_STEPS)
                                                    : 4 * m->base.n_groups * SV_STEPS;
     info->svc_guard = m->svc_guard;
+    info->svc_observed_err = m->svc_observed_err;
+    info->svc_observed_by_engine[0] = m->svc_observed_by_engine[0];
+    info->svc_observed_by_engine[1] = m->svc_observed_by_engine[1];
+    info->label_guard = m->base.label_guard;
+    info->label_observed_err = m->label_observed_err;
+    info->probe_rows = m->probe_rows;
+    info->guard_widened = m->guard_widened;
     info->device_bytes = m->device_bytes;
     info->rbf_engine = m->n_sv == 0 ? 0 : (m->mma.nb > 0 && m->tree_mode != 2 && m->rbf_engine != 1) ? 2 : 1;
     info->rbf_exp_per_row = info->rbf_engine == 2 ? m->mma.nb * m->mma.block_sv : ((m->n_sv + 3) / 4) * 4;

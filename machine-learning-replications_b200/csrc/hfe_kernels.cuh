@@ -418,10 +418,24 @@ __device__ __noinline__ bool eval_row_f64_warp(const ScoreParams& P, long long r
             if (nonfinite_flag) atomicOr(nonfinite_flag, HFE_ROW_NONFINITE);
         }
         store_row(P, row, r);
+        if (P.svc_dec) P.svc_dec[row] = part_svc + P.svc_intercept;
         label = r.z > 0 ? 1 : 0;
     }
     label = __shfl_sync(full_mask, label, 0);
     return P.y ? (label == (int)P.y[row]) : false;
+}
+
+// A row whose result hinges on a branch goes on the call's work list.  The checked build (-DHFE_BOUNDS_CHECK) also counts
+// the appends whose entry has been written in the reserved header word; hfe_fixup_kernel traps if that count differs from
+// the list length it sees -- the stand-in for a race checker on the hand-off between the two launches.
+__device__ __forceinline__ void worklist_append(const ScoreParams& P, long long row) {
+    const unsigned slot = atomicAdd(P.status + HFE_STATUS_LIST_LEN, 1u);
+    if (slot < (unsigned)HFE_WORKLIST_CAPACITY) P.status[HFE_STATUS_HEADER_WORDS + slot] = (unsigned)row;
+    else atomicOr(P.status, HFE_WORKLIST_OVERFLOW);
+#ifdef HFE_BOUNDS_CHECK
+    __threadfence();
+    atomicAdd(P.status + 3, 1u);
+#endif
 }
 
 // Outputs of one thread's R rows, the work list and the accuracy count -- shared by the fused pass and the streaming pass.
@@ -457,9 +471,7 @@ __device__ __forceinline__ void emit_rows(const ScoreParams& P, long long row0, 
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             if ((fixmask >> r) & 1u) {
-                unsigned slot = atomicAdd(P.status + HFE_STATUS_LIST_LEN, 1u);
-                if (slot < (unsigned)HFE_WORKLIST_CAPACITY) P.status[HFE_STATUS_HEADER_WORDS + slot] = (unsigned)(row0 + r);
-                else atomicOr(P.status, HFE_WORKLIST_OVERFLOW);
+                worklist_append(P, row0 + r);
             }
         }
     }
@@ -847,6 +859,11 @@ hfe_score_kernel(const __grid_constant__ ScoreParams P, int sv_bytes) {
         }
     }
     finish_rows_fast<R>(P, SVC, f_svc, zpart, p1, zfin, member[0], unc);
+    if (SVC && P.svc_dec) {                                             // creation-time guard probe only
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+            if (row0 + r < P.n) P.svc_dec[row0 + r] = f_svc[r];
+    }
     emit_rows<R, double>(P, row0, lane, full, nonfinite, fixmask, p1, zfin, member[0], unc);
     }   // tile loop
 }
@@ -962,6 +979,15 @@ hfe_stream_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__
             }
         }
         // every lane has read its part of this stage: hand the buffer back to the copy engine for the tile after next
+#ifdef HFE_BOUNDS_CHECK
+        // checked build: the tile is poisoned once every lane has read it and before the copy engine may refill it, so a
+        // read that runs ahead of the next tile's arrival (a wrong parity wait) sees NaN and trips the non-finite flag
+        __syncwarp();
+#pragma unroll
+        for (int f = 0; f < F; ++f) buf[f * (WARP_ROWS / 4)] = make_float4(__int_as_float(0x7FC00000), __int_as_float(0x7FC00000),
+                                                                         __int_as_float(0x7FC00000), __int_as_float(0x7FC00000));
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+#endif
         if (P.perm_col >= 0) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // our stores before the engine's
         __syncwarp();
         if (lane == 0 && tile + STREAM_STAGES * stride < n_tiles) issue(tile + STREAM_STAGES * stride, stage);
@@ -1011,6 +1037,7 @@ hfe_stream_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__
 __global__ void __launch_bounds__(BLOCK_THREADS)
 hfe_fixup_kernel(const __grid_constant__ ScoreParams P) {
     const unsigned count = min(P.status[HFE_STATUS_LIST_LEN], (unsigned)HFE_WORKLIST_CAPACITY);
+    HFE_ASSERT_IN(P.status[3] == P.status[HFE_STATUS_LIST_LEN]);        // every append had landed before this launch began
     const unsigned warp = (blockIdx.x * BLOCK_THREADS + threadIdx.x) >> 5;
     const unsigned n_warps = (gridDim.x * BLOCK_THREADS) >> 5;
     unsigned hits = 0;

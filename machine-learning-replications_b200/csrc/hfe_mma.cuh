@@ -217,7 +217,6 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
 
     if (warp < MMA_PRODUCER_WARPS) {
         // =========================== producers ====================================================================================
-        const bool has_lin = P.slot_lin >= 0;
         const int prow = tid;                                  // this thread's row of every tile
         auto fetch = [&](long long tile, float (&x)[F]) {
             // this row's 17 features: one coalesced 128-byte read per warp and column, all in flight at once
@@ -386,6 +385,7 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
                     if (P.out64) { P.out64[2 * row] = 1.0 - p1[r]; P.out64[2 * row + 1] = p1[r]; }
                     if (P.labels) P.labels[row] = lab;
                     if (P.decision) P.decision[row] = zfin[r];
+                    if (P.svc_dec) P.svc_dec[row] = f_svc[r];
                     if (P.meta) {
                         P.meta[row * P.n_members + P.slot_svc] = p_svc[r];
                         if (P.slot_gbt >= 0) P.meta[row * P.n_members + P.slot_gbt] = member[1][r];
@@ -393,9 +393,7 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
                     }
                 }
                 if (fix) {      // result hinges on a branch (or the row could not be scored here): the float64 fix-up redoes it
-                    const unsigned at = atomicAdd(P.status + HFE_STATUS_LIST_LEN, 1u);
-                    if (at < (unsigned)HFE_WORKLIST_CAPACITY) P.status[HFE_STATUS_HEADER_WORDS + at] = (unsigned)row;
-                    else atomicOr(P.status, HFE_WORKLIST_OVERFLOW);
+                    worklist_append(P, row);
                 }
                 if (P.y && P.score) hits += (valid && !fix && lab == P.y[row]) ? 1u : 0u;
             }

@@ -73,6 +73,7 @@ struct ScoreParams {
     unsigned char* labels;      // [n] or null
     double* decision;           // [n] or null
     double* meta;               // [n, n_members] or null
+    double* svc_dec;            // [n] or null: the SVC member's decision value as this pass computed it (guard probe)
     const unsigned char* y;     // [n] or null
     unsigned long long* score;  // [1] or null
     unsigned int* status;       // [HFE_STATUS_WORDS]
@@ -172,6 +173,13 @@ struct Model {
     int internal_of[F];           // internal feature of caller's column c
     double svc_guard = 0.0;       // assumed |error| of the float32 SVC decision value
     double gbt_guard = 0.0;       // assumed |error| of the float32 boosted raw score
+    double svc_guard_formula = 0.0;   // svc_guard as build_svc derives it from the dual coefficients (before any widening)
+    double guard_scale = 1.0;     // multiplies svc_guard_formula (hfe_model_calibrate_guards; 1 at creation)
+    double svc_observed_err = 0.0;    // creation-time probe: max |float32 - float64| of the SVC decision value
+    double svc_observed_by_engine[2] = {0.0, 0.0};   // ... per engine: SIMT loop, tensor cores
+    double label_observed_err = 0.0;  // ... and of the combiner's decision value, over rows the fast pass did not flag
+    int probe_rows = 0;           // rows the probe scored (0: no SVC member, or no device at plan time)
+    int guard_widened = 0;        // 1: the probe found svc_guard < 8 x observed and replaced it by 8 x observed
     ScoreParams base{};           // request fields zero; table pointers filled
     ForestParams forest{};        // n_chunks > 0: general trees can be walked out of shared memory
     int tree_engine = 0;          // 0 = automatic, 1 = node tables through L1 (__ldg), 2 = shared-memory chunks,
@@ -415,8 +423,11 @@ inline int build_svc(Model* m, const ParsedBlob& pb, uint32_t idx) {
     // float32 2^x must not overflow: 2c|z||s| <= 100  =>  c|z|^2 <= c*(100/(2c*max|s|))^2
     double zmax = 100.0 / (2.0 * P.c_log2 * std::max(max_norm, 1e-30));
     P.zz_limit = std::min(gamma * zmax * zmax, 600.0);          // compared against gamma*|z|^2
-    // assumed uncertainty of the float32 decision value (DESIGN.md "error budget"): ~20 sigma of the measured error
-    m->svc_guard = 3.5e-7 * std::sqrt(coef_l2) + 1e-7;
+    // assumed uncertainty of the float32 decision value (DESIGN.md "error budget"): ~40 sigma of the error measured on
+    // cohort rows, and >= 8 x the worst error the creation-time probe sees AT the support vectors (where the kernel values,
+    // hence the absolute rounding errors, are largest) for both fixture models -- the probe checks it for every model
+    m->svc_guard_formula = 8e-7 * std::sqrt(coef_l2) + 1e-7;
+    m->svc_guard = m->svc_guard_formula;
     P.n_groups = n_groups;
     P.sv_quads = 0;
     P.sv_bytes = (int)(tab.size() * sizeof(float4));
@@ -884,6 +895,30 @@ inline void permute_sections(ParsedBlob* pb, const int order[F], std::vector<std
     }
 }
 
+// Guard bands: how far the float32 decision values may be off, pushed through the Platt slope and the
+// combiner.  Called by build_model and again whenever the creation-time probe (hfe_api.cu: probe_guards) widens svc_guard.
+inline void derive_guards(Model* m) {
+    ScoreParams& P = m->base;
+    double slope = std::fabs(P.prob_a) * 0.25;                       // |d r / d f| <= |A|/4
+    P.solver_guard = std::fabs(P.prob_a) * m->svc_guard;             // in units of t = f*A + B
+    double w_svc = P.slot_svc >= 0 ? std::fabs(P.final_coef[P.slot_svc]) : 0.0;
+    P.label_guard = 2.0 * w_svc * slope * m->svc_guard + 1e-9 +
+                    (P.slot_gbt >= 0 ? std::fabs(P.final_coef[P.slot_gbt]) * 0.25 * m->gbt_guard : 0.0);
+    if (m->mma.nb > 0 && P.slot_lin >= 0) {
+        // tensor-core engine: the logistic member's dot product comes out of a float32 accumulator (|error| <~ 2^-23 of
+        // the largest partial sum) instead of a float64 FMA chain
+        double mag = std::fabs(m->mma.lin_base);
+        for (int d = 0; d < F; ++d) mag += 64.0 * std::fabs(P.lin_coef[d]);
+        P.label_guard += std::fabs(P.final_coef[P.slot_lin]) * 0.25 * 1.2e-7 * mag;
+    }
+    if (P.slot_svc < 0 && m->tree_mode != 2) {
+        // stacks scored by the streaming pass: float32 links (|error| <= 1.8e-7 each) and a float32 combiner logit
+        double w_sum = 0.0;
+        for (int i = 0; i < m->n_members; ++i) w_sum += std::fabs(P.final_coef[i]);
+        P.label_guard += w_sum * 1.8e-7 + (std::fabs(P.final_intercept) + w_sum) * 1.2e-7;
+    }
+}
+
 inline int build_model(const uint8_t* blob, size_t len, int device, Model** out) {
     ParsedBlob pb;
     int rc = parse_blob(blob, len, &pb);
@@ -979,9 +1014,6 @@ inline int build_model(const uint8_t* blob, size_t len, int device, Model** out)
             m->mma_img_host.shrink_to_fit();
         }
         P.final_intercept = fin->f64()[pb.n_members];
-        // guard bands: how far the float32 decision value may be off, pushed through the Platt slope
-        double slope = std::fabs(P.prob_a) * 0.25;                       // |d r / d f| <= |A|/4
-        P.solver_guard = std::fabs(P.prob_a) * m->svc_guard;             // in units of t = f*A + B
         if (P.slot_svc >= 0) {
             std::vector<double> edges = find_solver_edges();
             if (edges.size() > (size_t)MAX_EDGES) rc = fail(HFE_ERR_UNSUPPORTED, "coupling solver has too many edges");
@@ -990,22 +1022,7 @@ inline int build_model(const uint8_t* blob, size_t len, int device, Model** out)
                 for (size_t e = 0; e < edges.size(); ++e) P.edges[e] = edges[e];
             }
         }
-        double w_svc = P.slot_svc >= 0 ? std::fabs(P.final_coef[P.slot_svc]) : 0.0;
-        P.label_guard = 2.0 * w_svc * slope * m->svc_guard + 1e-9 +
-                        (P.slot_gbt >= 0 ? std::fabs(P.final_coef[P.slot_gbt]) * 0.25 * m->gbt_guard : 0.0);
-        if (m->mma.nb > 0 && P.slot_lin >= 0) {
-            // tensor-core engine: the logistic member's dot product comes out of a float32 accumulator (|error| <~ 2^-23 of
-            // the largest partial sum) instead of a float64 FMA chain
-            double mag = std::fabs(m->mma.lin_base);
-            for (int d = 0; d < F; ++d) mag += 64.0 * std::fabs(P.lin_coef[d]);
-            P.label_guard += std::fabs(P.final_coef[P.slot_lin]) * 0.25 * 1.2e-7 * mag;
-        }
-        if (P.slot_svc < 0 && m->tree_mode != 2) {
-            // stacks scored by the streaming pass: float32 links (|error| <= 1.8e-7 each) and a float32 combiner logit
-            double w_sum = 0.0;
-            for (int i = 0; i < m->n_members; ++i) w_sum += std::fabs(P.final_coef[i]);
-            P.label_guard += w_sum * 1.8e-7 + (std::fabs(P.final_intercept) + w_sum) * 1.2e-7;
-        }
+        derive_guards(m);
     }
     if (rc != HFE_OK) {
         for (void* p : m->allocations) cudaFree(p);

@@ -104,6 +104,13 @@ class HFStackB200:
         capi.check(self._lib.hfe_model_get_info(self._handle, C.byref(self.info)))
         return self
 
+    def calibrate_guards(self, formula_scale: float = 1.0):
+        """Re-run the creation-time guard probe (``hfe_model_calibrate_guards``) with the formula bands scaled by
+        ``formula_scale``; ``self.info`` then holds the bands in use and the errors the probe observed."""
+        capi.check(self._lib.hfe_model_calibrate_guards(self._handle, float(formula_scale)))
+        capi.check(self._lib.hfe_model_get_info(self._handle, C.byref(self.info)))
+        return self
+
     def set_tree_engine(self, engine):
         """``"auto"`` / ``"l1"`` / ``"smem"`` / ``"l1+l2window"``: how general boosted trees are walked (same results)."""
         capi.check(self._lib.hfe_model_set_tree_engine(self._handle, {"auto": 0, "l1": 1, "smem": 2, "l1+l2window": 3}[engine]))

@@ -18,7 +18,7 @@ def test_library_exports_every_declared_symbol(cuda_lib, pkg):
     for name in names:
         assert hasattr(cuda_lib, name), f"{name} is declared in hfe.h but not exported by libhfe.so"
     assert sorted(pkg.capi.EXPORTS) == names
-    assert cuda_lib.hfe_abi_version() == 1
+    assert cuda_lib.hfe_abi_version() == 2
 
 
 def test_bad_blob_is_refused_before_any_device_work(cuda_lib, pkg, published):

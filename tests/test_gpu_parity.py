@@ -777,3 +777,58 @@ def test_bounds_checked_build_on_small_and_ragged_cases(cuda_lib):
     res = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "sanitize_target.py")], env=env,
                          capture_output=True, text=True, timeout=600)
     assert res.returncode == 0 and "sanitize target done" in res.stdout, res.stderr[-2000:]
+
+
+def test_guard_probe_is_a_checked_contract(pkg, published, retrained, torch_cuda):
+    """hfe_model_create scores a probe batch (support vectors in raw units and crossovers of them) through every fast
+    engine and the float64 kernel; the handle reports what it saw and no band in use is below 8 x the observed error.
+    A formula band made 1000 x too narrow on purpose is widened by the probe instead of letting labels flip, and a
+    model whose dual coefficients are 1000 x larger (errors 1000 x larger) keeps its labels too."""
+    import copy
+    torch = torch_cuda
+    for case in (published, retrained):
+        clf = pkg.HFStackB200(case["blob"], device=0)
+        info = clf.info
+        assert info.probe_rows == 65536 and info.guard_widened == 0
+        assert 0.0 < info.svc_observed_err and 8.0 * info.svc_observed_err <= info.svc_guard
+        assert 0.0 < info.label_observed_err and 8.0 * info.label_observed_err <= info.label_guard
+        print(f"{case['name']}: svc_guard {info.svc_guard:.3e} / observed {info.svc_observed_err:.3e} = "
+              f"{info.svc_guard / info.svc_observed_err:.0f}x; label_guard {info.label_guard:.3e} / observed "
+              f"{info.label_observed_err:.3e} = {info.label_guard / info.label_observed_err:.0f}x")
+        wide = info.svc_guard
+        # the formula made far too optimistic: the probe has to put the band back above what it measures
+        clf.calibrate_guards(1e-3)
+        info = clf.info
+        assert info.guard_widened & 1 and info.svc_guard == 8.0 * info.svc_observed_err and info.svc_guard < wide
+        assert 8.0 * info.label_observed_err <= info.label_guard
+        n = 2_000_000
+        x = pkg.synth_rows_device(case["specs"], 41, 0, n)
+        lab = torch.empty(n, dtype=torch.uint8, device="cuda")
+        lab64 = torch.empty(n, dtype=torch.uint8, device="cuda")
+        for engine in ("simt", "tensor"):
+            clf.set_rbf_engine(engine)
+            clf.score_device(x, n=n, labels=lab)
+            clf.score_f64_device(x, n=n, labels=lab64)
+            torch.cuda.synchronize()
+            assert torch.equal(lab, lab64), engine
+        clf.set_rbf_engine("auto")
+        clf.calibrate_guards(1.0)
+        assert clf.info.guard_widened == 0 and clf.info.svc_guard == wide
+        clf.close()
+    # adversarial table: dual coefficients (and intercept) x 1000 -> decision values and their float32 error x 1000
+    arrays = copy.deepcopy(published["arrays"])
+    svc = arrays.members[0]
+    svc.dual_coef = svc.dual_coef * 1e3
+    svc.intercept = svc.intercept * 1e3
+    svc.prob_a = svc.prob_a / 1e3                         # keeps the Platt argument, hence the score distribution
+    big = pkg.HFStackB200.from_arrays(arrays)
+    ref = pkg.HFStackB200(published["blob"], device=0)
+    assert big.info.svc_observed_err > 100.0 * ref.info.svc_observed_err
+    assert 8.0 * big.info.svc_observed_err <= big.info.svc_guard
+    X = pkg.synth.host_rows(published["specs"], 43, 0, 20000).astype(np.float64)
+    assert np.array_equal(big.predict(X), so.predict(arrays, X))
+    dev, dev_labels = device_scores(big, X)
+    assert np.abs(dev - so.predict_proba(arrays, X)).max() <= PROBA_TOL
+    assert np.array_equal(big.classes_[dev_labels], so.predict(arrays, X))
+    big.close()
+    ref.close()
