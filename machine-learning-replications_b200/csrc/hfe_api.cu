@@ -212,7 +212,7 @@ int dispatch_score_inner(const Model* m, const ScoreParams& P, cudaStream_t stre
     }
     if (m->tree_mode == 2 && m->tree_engine == 2)
         return fail(HFE_ERR_UNSUPPORTED, "the shared-memory tree walk needs a stack without an SVC member, at most 256 "
-                                         "distinct (feature, threshold) pairs (255 per feature) and trees of at most 16 380 nodes");
+                                         "distinct (feature, threshold) pairs (255 per feature) and trees of at most 8 188 nodes");
     if (svc && m->mma.nb > 0 && m->tree_mode != 2 && m->rbf_engine != 1)
         return m->tree_mode == 0 ? launch_mma<0>(m, P, stream) : launch_mma<1>(m, P, stream);
     if (svc && m->rbf_engine == 2)

@@ -4,15 +4,19 @@
 // 15-25).  The fused kernel's general-tree walk reads 8-byte nodes through L1 (__ldg): the lanes of a warp sit at different
 // nodes of the same tree, and ncu shows 7.9 sectors per warp-wide load with the L1 tag stage as the bound.  Here
 //   * per feature the distinct thresholds of the whole forest are sorted (every schema feature takes a handful of values:
-//     a 2000-tree forest has ~90 thresholds in all); a row is turned into 17 bytes, per feature the number of thresholds
-//     below its value, kept in shared memory (one 32-bit word per thread and feature = its four rows);
-//   * a node is 4 bytes: feature | index of its threshold | in-tree index of the left child.  One level of the walk is a
-//     shared-memory load of the node, a byte load of the row's count for that feature, a compare and an add (leaves carry
-//     index 255, which no count exceeds, and point at themselves: a fixed-depth predicated walk needs no exit test).  The
-//     integer pipe runs at half rate on this part, so the step is kept to five integer instructions; address arithmetic
-//     goes to the FMA pipe (IMAD).  A first version that carried the comparisons as a 128-bit set in registers needed
-//     nine and was bound by that pipe at 55-58 M rows/s;
-//   * the node table streams through shared memory in chunks of up to 16 K nodes (64 KB, ~16 trees of the stress forest),
+//     a 2000-tree forest has ~90 thresholds in all); a row is turned into 17 counts, per feature the number of thresholds
+//     below its value, kept in shared memory as one 32-bit word each with the count in the top byte;
+//   * a node is 4 bytes: index of its threshold << 24 | feature << 16 | byte offset of the left child inside the staged
+//     chunk.  One level of the walk is: load the node; PRMT + IMAD make the address of the row's count for that feature;
+//     load it; ONE unsigned compare of the two words decides (count << 24 > node  <=>  count > threshold index, whatever
+//     the lower bits of the node are); one LOP3 turns the node into the child's address (the chunk buffers sit on 32 KB
+//     boundaries of the shared window, so base | offset); a predicated add takes the right child.  Leaves carry index 255,
+//     which no count exceeds, and their own offset: a fixed-depth walk needs no exit test.  Four instructions on the
+//     half-rate integer pipe, one on the FMA pipe, two loads.  Earlier versions, all bit-identical: counts as bytes with an
+//     in-tree child index (six integer + four IMAD instructions per level, 70 M rows/s on the stress forest); the
+//     comparisons carried as a 128-bit set in registers (nine integer instructions, 55-58 M rows/s); 8-byte nodes through
+//     L1 (48.7 M rows/s, and the same with the node table pinned in an L2 persisting window);
+//   * the node table streams through shared memory in chunks of up to 8 K nodes (32 KB, 8 trees of the stress forest),
 //     fetched by TMA bulk copies (cp.async.bulk + mbarrier) into two buffers: the whole block walks one chunk while the
 //     copy engine brings the next.  Breadth-first node order puts the first levels of a tree -- the ones all lanes visit --
 //     into distinct banks.
@@ -30,23 +34,29 @@ namespace hfe {
 constexpr int FOREST_TREES = HFE_FOREST_TREES;                         // trees walked side by side by one thread
 constexpr int FOREST_THREADS = 512;
 constexpr int FOREST_ROWS = FOREST_THREADS * ROWS_PER_THREAD;          // 2048 rows per block
-constexpr int FOREST_BUF_BYTES = (FOREST_CHUNK_NODES + 4) * 4;
-constexpr int FOREST_BIN_BYTES = F * FOREST_ROWS;                     // one byte per (feature, row of the block)
-constexpr size_t FOREST_SMEM_BYTES = 2 * (size_t)FOREST_BUF_BYTES + FOREST_BIN_BYTES + 64;
+constexpr int FOREST_BUF_BYTES = FOREST_CHUNK_NODES * 4;               // 32 KB, and the buffers are aligned to it
+constexpr int FOREST_BIN_BYTES = F * FOREST_ROWS * 4;                  // one word per (feature, row of the block)
+constexpr size_t FOREST_SMEM_BYTES = 227 * 1024;                       // bins | barriers | pad to a 32 KB boundary | two buffers
+static_assert((FOREST_BUF_BYTES & (FOREST_BUF_BYTES - 1)) == 0 && FOREST_BUF_BYTES <= 65536, "offset field: 16 bits, base | offset");
+// dynamic shared memory starts 1 KB into the shared window (the reserved kilobyte); the kernel checks what it finds
+static_assert(((1024 + FOREST_BIN_BYTES + 64 + FOREST_BUF_BYTES - 1) / FOREST_BUF_BYTES + 2) * FOREST_BUF_BYTES <= 1024 + (int)FOREST_SMEM_BYTES,
+              "bins, barriers and two aligned buffers fit");
 
 __global__ void __launch_bounds__(FOREST_THREADS, 1)
 hfe_forest_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ ForestParams Q) {
-    static_assert(FOREST_THREADS * 4 == FOREST_ROWS, "one 32-bit word of counts per thread and feature");
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    unsigned* s_buf[2] = {reinterpret_cast<unsigned*>(smem_raw), reinterpret_cast<unsigned*>(smem_raw + FOREST_BUF_BYTES)};
-    unsigned* s_bins = reinterpret_cast<unsigned*>(smem_raw + 2 * FOREST_BUF_BYTES);          // [F][FOREST_THREADS] words
-    unsigned long long* s_bar = reinterpret_cast<unsigned long long*>(smem_raw + 2 * FOREST_BUF_BYTES + FOREST_BIN_BYTES);
+    unsigned* s_bins = reinterpret_cast<unsigned*>(smem_raw);                                   // [F][R][FOREST_THREADS] words
+    unsigned long long* s_bar = reinterpret_cast<unsigned long long*>(smem_raw + FOREST_BIN_BYTES);
     constexpr int R = ROWS_PER_THREAD;
     const int tid = threadIdx.x, lane = tid & 31;
     const long long row0 = ((long long)blockIdx.x * FOREST_THREADS + tid) * R;
     const bool full = row0 + R <= P.n;
     const long long row_ld = row0 < P.n ? row0 : 0;
     const bool has_lin = P.slot_lin >= 0;
+    // the two chunk buffers: first 32 KB boundary of the shared window behind the barriers
+    const unsigned smem0 = (unsigned)__cvta_generic_to_shared(smem_raw);
+    const unsigned buf0 = (smem0 + (unsigned)FOREST_BIN_BYTES + 64u + (unsigned)FOREST_BUF_BYTES - 1u) & ~((unsigned)FOREST_BUF_BYTES - 1u);
+    if (buf0 + 2u * FOREST_BUF_BYTES > smem0 + (unsigned)FOREST_SMEM_BYTES) __trap();
 
     auto bar_addr = [&](int b) { return (unsigned)__cvta_generic_to_shared(s_bar + b); };
     // chunk c of the node table: trees [chunk_tree[c], chunk_tree[c + 1]); the copy starts 16-byte aligned
@@ -58,7 +68,7 @@ hfe_forest_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__
         const unsigned bar = bar_addr(c & 1);
         asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
         asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                     ::"r"((unsigned)__cvta_generic_to_shared(s_buf[c & 1])), "l"(Q.nodes4 + start), "r"(bytes), "r"(bar)
+                     ::"r"(buf0 + (unsigned)(c & 1) * FOREST_BUF_BYTES), "l"(Q.nodes4 + start), "r"(bytes), "r"(bar)
                      : "memory");
     };
     if (tid == 0) {
@@ -96,14 +106,19 @@ hfe_forest_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__
 #pragma unroll
             for (int r = 0; r < R; ++r) cnt[r] += xf[r] > thr ? 1u : 0u;
         }
-        s_bins[f * FOREST_THREADS + tid] = cnt[0] | (cnt[1] << 8) | (cnt[2] << 16) | (cnt[3] << 24);   // own slot: no barrier needed
+#pragma unroll
+        for (int r = 0; r < R; ++r) s_bins[(f * R + r) * FOREST_THREADS + tid] = cnt[r] << 24;   // own slots: no barrier needed
     }
     const bool nonfinite = !(finite_probe == 0.f);
     __syncthreads();                                                      // the barriers are initialised
 
     // ---- the walk: chunk by chunk, FOREST_TREES trees at a time ---------------------------------------
+    const unsigned bins0 = (unsigned)__cvta_generic_to_shared(s_bins) + (unsigned)tid * 4u;
+    float acc[R];                                   // float32 partial sums over groups of TREE_CHUNK trees, as the fused kernel forms them
+#pragma unroll
+    for (int r = 0; r < R; ++r) acc[r] = 0.f;
     for (int c = 0; c < Q.n_chunks; ++c) {
-        const unsigned* nodes = reinterpret_cast<const unsigned*>(smem_raw + (c & 1) * FOREST_BUF_BYTES);
+        const unsigned buf = buf0 + (unsigned)(c & 1) * FOREST_BUF_BYTES;
         {
             const unsigned bar = bar_addr(c & 1), parity = (unsigned)(c >> 1) & 1u;
             asm volatile(
@@ -118,40 +133,31 @@ hfe_forest_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__
         }
         const int t_begin = __ldg(Q.chunk_tree + c), t_end = __ldg(Q.chunk_tree + c + 1);
         const int origin = (int)chunk_start(c);
-        float acc[R];
-#pragma unroll
-        for (int r = 0; r < R; ++r) acc[r] = 0.f;
-        int folded = 0;
         for (int t = t_begin; t < t_end; t += FOREST_TREES) {
             // FOREST_TREES trees at a time: FOREST_TREES x R independent chains per thread (the walk is bound by the latency of
-            // one level: shared-memory load -> bit test -> add); a short last group repeats its last tree and drops the copy
-            unsigned base[FOREST_TREES];
-            int off[FOREST_TREES], depth = 0;
+            // one level: node load -> count load -> compare -> add); a short last group repeats its last tree and drops the copy
+            int depth = 0;
+            unsigned at[FOREST_TREES][R];                 // shared-window address of each chain's node
 #pragma unroll
             for (int k = 0; k < FOREST_TREES; ++k) {
                 const int tk = min(t + k, t_end - 1);
-                off[k] = __ldg(P.tree_off + tk);
-                base[k] = (unsigned)__cvta_generic_to_shared(nodes) + (unsigned)(off[k] - origin) * 4u;
+                const unsigned root = buf + (unsigned)(__ldg(P.tree_off + tk) - origin) * 4u;
                 depth = max(depth, (int)__ldg(P.tree_depth + tk));
+#pragma unroll
+                for (int r = 0; r < R; ++r) at[k][r] = root;
             }
-            unsigned at[FOREST_TREES][R];                 // byte address of each chain's node
-#pragma unroll
-            for (int k = 0; k < FOREST_TREES; ++k)
-#pragma unroll
-                for (int r = 0; r < R; ++r) at[k][r] = base[k];
-            const unsigned bins0 = (unsigned)__cvta_generic_to_shared(s_bins) + (unsigned)tid * 4u;
             for (int lvl = 0; lvl < depth; ++lvl) {
 #pragma unroll
                 for (int r = 0; r < R; ++r) {
 #pragma unroll
                     for (int k = 0; k < FOREST_TREES; ++k) {
-                        unsigned d, c;
+                        unsigned d, w;
                         asm("ld.shared.u32 %0, [%1];" : "=r"(d) : "r"(at[k][r]));
-                        // node: feature | threshold index | in-tree index of the left child; the row's count for that feature is
-                        // byte r of the thread's word in row `feature` of the table
-                        asm("ld.shared.u8 %0, [%1];" : "=r"(c) : "r"((d >> 24) * (unsigned)(FOREST_THREADS * 4) + (bins0 + r)));
-                        const unsigned step = c > __byte_perm(d, 0u, 0x4442u) ? 4u : 0u;
-                        at[k][r] = (d & 0xFFFFu) * 4u + base[k] + step;
+                        asm("ld.shared.u32 %0, [%1];" : "=r"(w)
+                            : "r"(__byte_perm(d, 0u, 0x4442u) * (unsigned)(R * FOREST_THREADS * 4) + bins0 + (unsigned)(r * FOREST_THREADS * 4)));
+                        unsigned next = (d & 0xFFFFu) | buf;
+                        if (w > d) next += 4u;
+                        at[k][r] = next;
                     }
                 }
             }
@@ -160,20 +166,19 @@ hfe_forest_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__
                 const bool live = t + k < t_end;
 #pragma unroll
                 for (int r = 0; r < R; ++r)
-                    if (live) acc[r] += __ldg(P.value32 + off[k] + (int)((at[k][r] - base[k]) >> 2));
+                    if (live) acc[r] += __ldg(P.value32 + origin + (int)((at[k][r] - buf) >> 2));
             }
-            folded += FOREST_TREES;
-            if (folded >= TREE_CHUNK) {                                   // float32 partial sums never span more than 16 trees
+            if ((min(t + FOREST_TREES, t_end) / TREE_CHUNK) != (t / TREE_CHUNK)) {   // float32 partial sums never span more than 16 trees
 #pragma unroll
                 for (int r = 0; r < R; ++r) { raw[r] += (double)acc[r]; acc[r] = 0.f; }
-                folded = 0;
             }
         }
-#pragma unroll
-        for (int r = 0; r < R; ++r) raw[r] += (double)acc[r];
         __syncthreads();                                                  // everyone is done with this buffer
         if (tid == 0 && c + 2 < Q.n_chunks) issue_chunk(c + 2);
     }
+
+#pragma unroll
+    for (int r = 0; r < R; ++r) raw[r] += (double)acc[r];
 
     // ---- links, combiner, outputs: the fused kernel's epilogue without an SVC member ---------------------------------------------
     double zpart[R], member[3][R];

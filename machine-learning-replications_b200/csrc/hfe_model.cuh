@@ -146,14 +146,14 @@ struct MmaParams {
 
 // General boosted trees walked out of shared memory (hfe_forest.cuh).  Per feature the distinct thresholds of the whole
 // forest are sorted; a row carries, per feature, the number of thresholds below its value (one byte), and a node is 4
-// bytes -- feature, index of its threshold in that feature's list, in-tree index of the left child -- so a level of the
-// walk is two shared-memory loads and a handful of integer instructions.
+// bytes -- index of its threshold in that feature's list, feature, byte offset of the left child inside the staged chunk -- so
+// a level of the walk is two shared-memory loads and a handful of integer instructions.
 constexpr int FOREST_MAX_THR = 256;            // distinct (feature, threshold) pairs of the forest, at most 255 per feature
-constexpr int FOREST_CHUNK_NODES = 16384;      // nodes staged per chunk (64 KB); two chunks are resident
+constexpr int FOREST_CHUNK_NODES = 8192;       // nodes staged per chunk (32 KB); two chunks are resident
 
 struct ForestParams {
-    const unsigned* nodes4;         // per node: feature << 24 | threshold index << 16 | in-tree index of the left child
-                                    // (leaves: feature 0, index 255 -- never exceeded -- and their own index)
+    const unsigned* nodes4;         // per node: threshold index << 24 | feature << 16 | byte offset of the left child from
+                                    // the start of its chunk's copy (leaves: index 255 -- never exceeded -- and their own offset)
     const int* chunk_tree;          // [n_chunks + 1] first tree of each chunk
     int n_chunks;
     int n_thr;
@@ -801,14 +801,16 @@ inline int build_gbt(Model* m, const ParsedBlob& pb, uint32_t idx) {
                     chunk_tree.push_back(t);
                     chunk_start = base;
                 }
+                const int64_t origin = chunk_start & ~(int64_t)3;                          // first node of the chunk's copy
                 for (int i = 0; i < cnt; ++i) {
                     const int64_t q = base + i;
                     const uint32_t child = nodes[q].y & 0xFFFFFFu;
                     if (child == (uint32_t)q) {
-                        nodes4[q] = (255u << 16) | (uint32_t)i;                           // leaf: the test never holds
+                        nodes4[q] = (255u << 24) | (uint32_t)((q - origin) * 4);          // leaf: the test never holds
                     } else {
                         const uint32_t f = nodes[q].y >> 24;
-                        nodes4[q] = (f << 24) | ((uint32_t)thr_id[{(int)f, key_of(nodes[q].x)}] << 16) | (child - (uint32_t)base);
+                        nodes4[q] = ((uint32_t)thr_id[{(int)f, key_of(nodes[q].x)}] << 24) | (f << 16) |
+                                    (uint32_t)(((int64_t)child - origin) * 4);
                     }
                 }
             }
