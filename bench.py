@@ -391,11 +391,13 @@ def leg_stress(ctx, arrays, x, n, hbm_peak):
     return res
 
 
-def leg_perm(ctx, clf, x, n):
-    """BASELINE config 5: permutation importance, 17 columns x 5 repeats + baseline = 86 passes over 1 M rows."""
+def leg_perm(ctx, clf, specs, n):
+    """BASELINE config 5: permutation importance, 17 columns x 5 repeats + baseline = 86 passes over 1 M rows.
+    Every rank holds the same cohort (global rows [0, 1 M)) and scores its share of the 86 passes."""
     torch = ctx.torch
     pkg = ctx.pkg
     rows = min(n, 1_000_000)
+    x = pkg.synth_rows_device(specs, SEED, 0, rows, device=ctx.local_rank)
     lab = torch.empty(rows, dtype=torch.uint8, device=ctx.dev)
     clf.score_device(x, n=rows, labels=lab)
     flip = torch.from_numpy(pkg.synth.hash_u32(99, np.arange(rows), 251) < 2 ** 29).to(ctx.dev)   # 12.5 % label noise
@@ -484,7 +486,7 @@ def run_ours(args):
     if "stress" in want:
         legs["stress"] = leg_stress(ctx, arrays, x, n, hbm_peak)
     if "perm" in want:
-        legs["perm_importance"] = leg_perm(ctx, clf, x, n)
+        legs["perm_importance"] = leg_perm(ctx, clf, specs, n)
 
     if rank != 0:
         return

@@ -632,11 +632,14 @@ struct Mt19937 {
         mt[0] = seed;
         for (int i = 1; i < 624; ++i) mt[i] = 1812433253u * (mt[i - 1] ^ (mt[i - 1] >> 30)) + (uint32_t)i;
     }
-    void refill() {
-        for (int k = 0; k < 624; ++k) {
-            const uint32_t yv = (mt[k] & 0x80000000u) | (mt[(k + 1) % 624] & 0x7FFFFFFFu);
-            mt[k] = mt[(k + 397) % 624] ^ (yv >> 1) ^ ((yv & 1u) ? 0x9908B0DFu : 0u);
-        }
+    static uint32_t twist(uint32_t hi, uint32_t lo, uint32_t far) {
+        const uint32_t yv = (hi & 0x80000000u) | (lo & 0x7FFFFFFFu);
+        return far ^ (yv >> 1) ^ ((yv & 1u) ? 0x9908B0DFu : 0u);
+    }
+    void refill() {                      // genrand_int32's block update, split so that no index wraps inside a loop
+        for (int k = 0; k < 227; ++k) mt[k] = twist(mt[k], mt[k + 1], mt[k + 397]);
+        for (int k = 227; k < 623; ++k) mt[k] = twist(mt[k], mt[k + 1], mt[k - 227]);
+        mt[623] = twist(mt[623], mt[0], mt[396]);
         pos = 0;
     }
     uint32_t next() {
@@ -656,25 +659,41 @@ int hfe_perm_indices(uint32_t seed, int64_t n, int32_t n_repeats, int32_t* out) 
         return fail(HFE_ERR_INVALID_ARGUMENT, "bad permutation request");
     try {
         Mt19937 rng(seed);
-        std::vector<int32_t> idx((size_t)n);
+        std::vector<int32_t> idx((size_t)n), snap[2];
         for (int64_t i = 0; i < n; ++i) idx[(size_t)i] = (int32_t)i;
+        std::thread composer;
+        constexpr int AHEAD = 256;
+        uint32_t js[AHEAD];
         for (int32_t r = 0; r < n_repeats; ++r) {
-            // RandomState.shuffle: for i = n-1 .. 1: j = random_interval(i) (masked rejection on 32-bit draws); swap
-            for (int64_t i = n - 1; i >= 1; --i) {
-                uint32_t mask = (uint32_t)i;
-                mask |= mask >> 1; mask |= mask >> 2; mask |= mask >> 4; mask |= mask >> 8; mask |= mask >> 16;
-                uint32_t j;
-                while ((j = rng.next() & mask) > (uint32_t)i) {}
-                std::swap(idx[(size_t)i], idx[j]);
+            // RandomState.shuffle: for i = n-1 .. 1: j = random_interval(i) (masked rejection on 32-bit draws); swap.
+            // The draws do not depend on the array, so they are made a block ahead and their targets prefetched: the swap
+            // chain itself is serial, and on a vector of millions it would otherwise wait for memory at every step.
+            for (int64_t i = n - 1; i >= 1; i -= AHEAD) {
+                const int cnt = (int)std::min<int64_t>(AHEAD, i);
+                for (int k = 0; k < cnt; ++k) {
+                    const uint32_t top = (uint32_t)(i - k);
+                    const uint32_t mask = 0xFFFFFFFFu >> __builtin_clz(top);
+                    uint32_t j;
+                    while ((j = rng.next() & mask) > top) {}
+                    js[k] = j;
+                    __builtin_prefetch(&idx[j], 1);
+                }
+                for (int k = 0; k < cnt; ++k) std::swap(idx[(size_t)(i - k)], idx[js[k]]);
             }
-            // the shuffled vector is applied to the already permuted column: effective source index e_r = e_{r-1}[idx]
+            // the shuffled vector is applied to the already permuted column: effective source index e_r = e_{r-1}[idx].
+            // That gather runs on a second thread, from a snapshot, while the next shuffle proceeds.
             int32_t* cur = out + (size_t)r * (size_t)n;
+            if (composer.joinable()) composer.join();
             if (r == 0) std::memcpy(cur, idx.data(), (size_t)n * sizeof(int32_t));
             else {
+                std::vector<int32_t>& sn = snap[r & 1];
+                sn = idx;
                 const int32_t* prev = cur - n;
-                for (int64_t i = 0; i < n; ++i) cur[i] = prev[idx[(size_t)i]];
+                const int32_t* src = sn.data();
+                composer = std::thread([cur, prev, src, n] { for (int64_t i = 0; i < n; ++i) cur[i] = prev[src[i]]; });
             }
         }
+        if (composer.joinable()) composer.join();
     } catch (const std::exception& e) {
         return fail(HFE_ERR_INVALID_ARGUMENT, std::string("out of host memory: ") + e.what());
     }

@@ -46,5 +46,5 @@ def test_native_shuffles_are_numpys(pkg, cuda_lib):
     """hfe_perm_indices restates RandomState(seed).shuffle (legacy MT19937, masked rejection) and scikit-learn's cumulative
     use of it (SK/inspection/_permutation_importance.py:66-74): bit for bit the numpy restatement, hence scikit-learn's."""
     insp = pkg.inspection
-    for n, reps, seed in ((0, 2, 1), (1, 3, 5), (2, 2, 7), (3, 4, 0), (257, 5, 4294967295), (50_000, 5, 2020), (65_537, 2, 123456789)):
+    for n, reps, seed in ((0, 2, 1), (1, 3, 5), (2, 2, 7), (3, 4, 0), (255, 3, 9), (256, 3, 9), (257, 5, 4294967295), (513, 2, 77), (50_000, 5, 2020), (65_537, 2, 123456789)):
         assert np.array_equal(insp.native_shuffled_indices(n, reps, seed), insp.shuffled_indices(n, reps, seed)), (n, seed)
