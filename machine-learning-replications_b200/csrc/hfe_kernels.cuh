@@ -163,51 +163,30 @@ __device__ __forceinline__ void finish_rows_fast(const ScoreParams& P, bool has_
 #pragma unroll
     for (int r = 0; r < R; ++r) { uncertain[r] = false; p_svc[r] = 0.0; }
     if (has_svc) {
-        double q00[R], q11[R], q01[R], iq00[R], iq11[R], a0[R], a1[R];
-        bool done[R];
+        // Platt, clamp and the two-class coupling sweeps (svm.cpp:2035-2107, 2932-2941) are one fixed function of
+        // t = f*A + B: it is read from the table build_model uploads (hfe_solver.cuh: a cubic per 1/128 of t and side of the
+        // sweep-count edge, fit error ~3e-11) instead of being iterated per row.  Rows within the guard band of an edge go to
+        // the exact path as before.
+        double fr[R];
+        int cell[R];
+        bool nan_t[R];
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            double t = fma(f_svc[r], P.prob_a, P.prob_b);
-            double e = exp_neg_fast(-fabs(t));
-            double inv = rcp_fast(1.0 + e);
-            double r01 = t >= 0 ? e * inv : inv;                      // svm.cpp:2035-2043
-            r01 = fmin(fmax(r01, 1e-7), 1.0 - 1e-7);                  // svm.cpp:2932-2941
-            double r10 = 1.0 - r01;
-            q00[r] = r10 * r10; q11[r] = r01 * r01; q01[r] = -r10 * r01;
-            iq00[r] = rcp_fast(q00[r]); iq11[r] = rcp_fast(q11[r]);
-            a0[r] = 0.5; a1[r] = 0.5;
-            done[r] = !(t == t);                                      // NaN rows skip the solver
-            double nearest = 1e300;
-            for (int k = 0; k < P.n_edges; ++k) nearest = fmin(nearest, fabs(t - P.edges[k]));
-            uncertain[r] = !(nearest >= P.solver_guard);
-        }
-#pragma unroll 1
-        for (int iter = 0; iter < 100; ++iter) {                      // svm.cpp:2046-2107, k = 2
-            bool all_done = true;
-#pragma unroll
-            for (int r = 0; r < R; ++r) {
-                if (done[r]) continue;
-                double qp0 = q00[r] * a0[r] + q01[r] * a1[r];
-                double qp1 = q01[r] * a0[r] + q11[r] * a1[r];
-                double pqp = a0[r] * qp0 + a1[r] * qp1;
-                double err = fmax(fabs(qp0 - pqp), fabs(qp1 - pqp));
-                if (err < 0.005 / 2) { done[r] = true; continue; }
-                all_done = false;
-                double diff = (pqp - qp0) * iq00[r];
-                double inv = rcp_fast(1.0 + diff);
-                a0[r] = (a0[r] + diff) * inv;
-                a1[r] = a1[r] * inv;
-                pqp = (pqp + diff * (diff * q00[r] + 2.0 * qp0)) * inv * inv;
-                qp1 = (qp1 + diff * q01[r]) * inv;
-                diff = (pqp - qp1) * iq11[r];
-                inv = rcp_fast(1.0 + diff);
-                a1[r] = (a1[r] + diff) * inv;
-                a0[r] = a0[r] * inv;
-            }
-            if (all_done) break;
+            const double t = fma(f_svc[r], P.prob_a, P.prob_b);
+            nan_t[r] = !(t == t);
+            const double u = (fmin(fmax(t, COUPLING_T_LO), COUPLING_T_HI) - COUPLING_T_LO) * (double)COUPLING_CELLS_PER_UNIT;
+            cell[r] = min(__double2int_rz(u), COUPLING_CELLS - 1);            // (NaN -> cell 0; such rows are flagged elsewhere)
+            fr[r] = u - (double)cell[r];
         }
 #pragma unroll
-        for (int r = 0; r < R; ++r) p_svc[r] = a1[r];
+        for (int r = 0; r < R; ++r) {
+            const double edge = __ldg(P.coupling_edge + cell[r]);
+            const double dist = fr[r] - edge;
+            uncertain[r] = nan_t[r] || !(fabs(dist) * (1.0 / COUPLING_CELLS_PER_UNIT) >= P.solver_guard);
+            const double2* q = reinterpret_cast<const double2*>(P.coupling_coef + (size_t)cell[r] * 8 + (dist >= 0.0 ? 4 : 0));
+            const double2 c01 = __ldg(q), c23 = __ldg(q + 1);
+            p_svc[r] = fma(fma(fma(c23.y, fr[r], c23.x), fr[r], c01.y), fr[r], c01.x);
+        }
     }
 #pragma unroll
     for (int r = 0; r < R; ++r) {

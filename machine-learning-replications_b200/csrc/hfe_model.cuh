@@ -92,6 +92,8 @@ struct ScoreParams {
     double zz_limit;            // rows with gamma*|z|^2 above this go to the float64 path (float32 2^x range)
     double solver_guard;        // Platt argument within this of a solver edge => the solver's branch is uncertain
     double edges[MAX_EDGES];    // values of t = f*A+B where the coupling solver's sweep count changes
+    const double* coupling_coef;    // the coupling map as a table (hfe_solver.cuh): [cells][2][4] cubic coefficients
+    const double* coupling_edge;    // [cells] local coordinate of the cell's edge (1e9: none)
     int n_edges;
     int pad_edges_;
     double label_guard;         // |z_final| below this => hard label is uncertain
@@ -1022,6 +1024,10 @@ inline int build_model(const uint8_t* blob, size_t len, int device, Model** out)
             else {
                 P.n_edges = (int)edges.size();
                 for (size_t e = 0; e < edges.size(); ++e) P.edges[e] = edges[e];
+                const CouplingTable& tab = coupling_table(edges);
+                if (!tab.ok) rc = fail(HFE_ERR_UNSUPPORTED, "coupling table: fit error above 1e-9 or two solver edges in one cell");
+                if (rc == HFE_OK) rc = upload(m, tab.coef, &P.coupling_coef);
+                if (rc == HFE_OK) rc = upload(m, tab.edge, &P.coupling_edge);
             }
         }
         derive_guards(m);
