@@ -38,6 +38,10 @@
 // the exponent warps it kept them off the MUFU pipe a quarter of the time).
 #pragma once
 
+#ifndef HFE_ISSUE_MODE
+#define HFE_ISSUE_MODE 2          // what the issuing warp does when neither stream is ready: 0 spin, 1 nanosleep, 2 block on the stream further behind (measured: 1.584 / 1.581 / 1.548 ms)
+#endif
+
 #include <cuda_bf16.h>
 
 #include "hfe_kernels.cuh"
@@ -47,7 +51,16 @@ namespace hfe {
 constexpr int MMA_TILE_ROWS = 128;
 constexpr int MMA_PRODUCER_WARPS = 4, MMA_FINISH_WARPS = 4, MMA_EPI_WARPS = 8;
 constexpr int MMA_EPI_WARP0 = MMA_PRODUCER_WARPS + MMA_FINISH_WARPS;             // exponent warps 8..15
-constexpr int MMA_THREADS = 32 * (MMA_PRODUCER_WARPS + MMA_FINISH_WARPS + MMA_EPI_WARPS);   // 512
+constexpr int MMA_ISSUE_WARP = MMA_PRODUCER_WARPS + MMA_FINISH_WARPS + MMA_EPI_WARPS;                     // warp 16: tcgen05.mma issue
+constexpr int MMA_THREADS = 32 * (MMA_ISSUE_WARP + 4);          // 640: the issuing warp brings its warpgroup (three idle warps)
+// Registers per thread and warpgroup (setmaxnreg; the kernel starts every thread at 96 = what 640 threads leave of 64 K):
+// the float64 finishing code wants the most, the issuing warpgroup next to none.  What one group gives up another can take:
+// the sum over the five groups must not exceed 5 x 96 (the pool is what the CTA was launched with; asking for more blocks forever).
+#ifndef HFE_MMA_REGS
+#define HFE_MMA_REGS 80, 144, 104, 48
+#endif
+constexpr int MMA_REGS[4] = {HFE_MMA_REGS};               // producers, finishers, exponent warps (each of two groups), issue group
+static_assert(MMA_REGS[0] + MMA_REGS[1] + 2 * MMA_REGS[2] + MMA_REGS[3] <= 5 * 96, "register pool of the CTA");
 constexpr int MMA_A_STAGES = 5;                          // two tiles in the tensor core / exponent warps, three produced ahead
 constexpr int MMA_A_CHUNKS = 12;                         // 16-byte K chunks per row: H0 H1 H2 0 | M0 M1 M2 0 | L0 L1 L2 0
 constexpr int MMA_A_STAGE_BYTES = (MMA_TILE_ROWS / 8) * MMA_A_CHUNKS * 128;                   // 24 576
@@ -84,6 +97,22 @@ __device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
             else if (clock64() - t0 > 4000000000LL) __trap();
         }
     }
+}
+__device__ __forceinline__ bool mbar_test(unsigned bar, unsigned parity) {       // has the phase with this parity completed?
+    unsigned done;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    return done != 0;
+}
+template <int REGS, bool INC>
+__device__ __forceinline__ void set_max_regs() {          // all four warps of a warpgroup, converged
+    static_assert(REGS % 8 == 0 && REGS >= 24 && REGS <= 256, "setmaxnreg operand");
+    if (INC) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(REGS));
+    else asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(REGS));
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -217,6 +246,7 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
 
     if (warp < MMA_PRODUCER_WARPS) {
         // =========================== producers ====================================================================================
+        set_max_regs<MMA_REGS[0], MMA_REGS[0] >= 96>();
         const int prow = tid;                                  // this thread's row of every tile
         auto fetch = [&](long long tile, float (&x)[F]) {
             // this row's 17 features: one coalesced 128-byte read per warp and column, all in flight at once
@@ -336,6 +366,7 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
             mbar_wait(bar(B_AEMPTY + (int)(k % MMA_A_STAGES)), (unsigned)((k / MMA_A_STAGES) & 1));
     } else if (warp < MMA_EPI_WARP0) {
         // =========================== finishing warps: the float64 epilogue of every row ===========================================
+        set_max_regs<MMA_REGS[1], MMA_REGS[1] >= 96>();
         // thread = row; the rows of four consecutive tiles are finished together, so four independent float64 chains
         // (Platt, clamp, coupling, links, combiner: the SIMT kernel's epilogue code) are interleaved
         constexpr int R = MMA_TAIL_ROWS;
@@ -403,19 +434,15 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
                 if (lane == 0 && hits) atomicAdd(P.score, (unsigned long long)hits);
             }
         }
-    } else {
-        // =========================== exponent warps ================================================================================
-        const int s = (warp - MMA_EPI_WARP0) >> 2;                   // stream
-        const int row_in_tile = (warp & 3) * 32 + lane;              // TMEM lane = row of the tile (warp % 4 picks the lane quarter)
-        const unsigned lane_base = tmem_base + ((unsigned)((warp & 3) * 32) << 16);
+    } else if (warp >= MMA_ISSUE_WARP) {
+        // =========================== MMA issue: one warp, converged, one elected lane ============================================
+        set_max_regs<MMA_REGS[3], false>();               // the whole warpgroup gives its registers away; three warps then idle
+        if (warp == MMA_ISSUE_WARP) {
+        // Blocks of a stream's tiles are issued in order, each into the region the stream's four exponent warps have just
+        // drained (the first two of a stream go into its still empty regions); the two streams are served as their regions
+        // come free.  Kept apart from the exponent warps: issued by them in turn, the issuing warp sat 17 % of its time
+        // waiting for its slowest peer and started its own next block late -- so the next issuer waited for it.
         mbar_wait(bar(B_W), 0);
-        const float* s_coef = reinterpret_cast<const float*>(s_w + (size_t)nb * bsv * (MMA_B_CHUNKS * 16));
-        const int steps = bsv >> 4;
-        // ---- MMA issue, in turn by the four warps of the stream (converged; one elected lane issues): block u is issued by
-        //      warp u % 4.  A fixed issuer would fall behind its three peers by the issue time in every block and they would wait
-        //      for it; taking turns, every warp is late once in four blocks and the two-region pipeline absorbs it.  Blocks of the stream's tiles are issued in order, each into the
-        //      region the four warps have just drained (the first two go into the still empty regions). ----------------------
-        const unsigned quarter = (unsigned)warp & 3u;
         // instruction descriptor (cute::UMMA::InstrDescriptor): D float32, A and B bfloat16, both K-major, N = bsv, M = 128
         const unsigned idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((unsigned)(bsv >> 3) << 17) | ((128u >> 4) << 24);
         // descriptors are built once; per instruction only the 14-bit start-address field (16-byte units, low word) moves
@@ -423,25 +450,39 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
         const unsigned long long a_desc0 = umma_desc(smem_addr(s_a), 128, a_sbo);
         const unsigned long long b_desc0 = umma_desc(smem_addr(s_w), 128, b_sbo);
         const unsigned b_blk_units = (unsigned)(bsv / 8) * (b_sbo / 16);          // descriptor units per block of support vectors
-        long long iss_tile = blockIdx.x + (long long)s * gridDim.x;
-        unsigned iss_i = (unsigned)s, iss_use = 0, iss_stage = (unsigned)s % MMA_A_STAGES, iss_phase = 0;   // phase of a_full[iss_stage]
-        int iss_blk = 0;
-        bool iss_ext = false;
-        auto issue_next = [&](bool mine) {           // every warp of the stream keeps the issue state; `mine` issues
-            if (iss_tile >= n_tiles) return;
-            if (mine) {
-            MMA_TRACE_WAIT(8, mbar_wait(bar(B_AFULL + iss_stage), iss_phase));
-            iss_ext = (s_ext[iss_stage * 4 + 0] | s_ext[iss_stage * 4 + 1] | s_ext[iss_stage * 4 + 2] | s_ext[iss_stage * 4 + 3]) != 0;
+        struct IssueState {
+            long long tile;
+            unsigned i, use, stage, phase;      // CTA-local tile number, blocks issued so far, A stage and the phase of its a_full
+            int blk;
+            bool ext;
+        } st[2];
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+            st[s].tile = blockIdx.x + (long long)s * gridDim.x;
+            st[s].i = (unsigned)s;
+            st[s].use = 0;
+            st[s].stage = (unsigned)s % MMA_A_STAGES;
+            st[s].phase = 0;
+            st[s].blk = 0;
+            st[s].ext = false;
+        }
+        auto try_issue = [&](IssueState& q, const int s) -> bool {
+            const unsigned reg = q.use & 1u;
+            // the region must have been drained (block use - 2) and, for the first block of a tile, the A stage filled
+            if (q.use >= 2 && !mbar_test(bar(B_ACCEMPTY + 2 * s + reg), ((q.use >> 1) - 1u) & 1u)) return false;
+            if (q.blk == 0) {
+                if (!mbar_test(bar(B_AFULL + q.stage), q.phase)) return false;
+                q.ext = (s_ext[q.stage * 4 + 0] | s_ext[q.stage * 4 + 1] | s_ext[q.stage * 4 + 2] | s_ext[q.stage * 4 + 3]) != 0;
+            }
             tc_fence_after();
-            const unsigned reg = iss_use & 1u;
             const unsigned d = tmem_base + (2u * s + reg) * MMA_REGION_COLS;
-            const unsigned long long a0 = a_desc0 + iss_stage * (MMA_A_STAGE_BYTES / 16);
-            const unsigned long long b0 = b_desc0 + (unsigned)iss_blk * b_blk_units;
+            const unsigned long long a0 = a_desc0 + q.stage * (MMA_A_STAGE_BYTES / 16);
+            const unsigned long long b0 = b_desc0 + (unsigned)q.blk * b_blk_units;
             // a K-step takes two adjacent 16-byte chunks of each operand (chunks are 128 bytes = 8 descriptor units apart).
             // A chunks  H0 H1 H2 0 | M0 M1 M2 0 | L0 L1 L2 0      B chunks  WL0 WL1 WL2 WM0 WM1 WM2 WH0 WH1 WH2 0
             // The second chunk of the (H2 0) steps is zero on the A side, so whatever follows on the B side does not matter.
             // Smallest products first.
-            if (iss_ext) {
+            if (q.ext) {
                 umma_bf16(d, a0 + 8 * 8, b0 + 6 * 8, idesc, 0u);              // (L0 L1).(WH0 WH1)        2^-16
                 umma_bf16(d, a0 + 10 * 8, b0 + 8 * 8, idesc, 1u);             // (L2 0).(WH2 .)
                 umma_bf16(d, a0 + 4 * 8, b0 + 3 * 8, idesc, 1u);              // (M0 M1).(WM0 WM1)        2^-16
@@ -449,35 +490,57 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
                 umma_bf16(d, a0 + 4 * 8, b0 + 6 * 8, idesc, 1u);              // (M0 M1).(WH0 WH1)        2^-8
                 umma_bf16(d, a0 + 6 * 8, b0 + 8 * 8, idesc, 1u);              // (M2 0).(WH2 .)
             }
-            umma_bf16(d, a0 + 0 * 8, b0 + 0 * 8, idesc, iss_ext ? 1u : 0u);   // (H0 H1).(WL0 WL1)        2^-16
+            umma_bf16(d, a0 + 0 * 8, b0 + 0 * 8, idesc, q.ext ? 1u : 0u);     // (H0 H1).(WL0 WL1)        2^-16
             umma_bf16(d, a0 + 2 * 8, b0 + 2 * 8, idesc, 1u);                  // (H2 0).(WL2 .)
             umma_bf16(d, a0 + 0 * 8, b0 + 3 * 8, idesc, 1u);                  // (H0 H1).(WM0 WM1)        2^-8
             umma_bf16(d, a0 + 2 * 8, b0 + 5 * 8, idesc, 1u);                  // (H2 0).(WM2 .)
             umma_bf16(d, a0 + 0 * 8, b0 + 6 * 8, idesc, 1u);                  // (H0 H1).(WH0 WH1)        1
             umma_bf16(d, a0 + 2 * 8, b0 + 8 * 8, idesc, 1u);                  // (H2 0).(WH2 .)
             tc_commit(bar(B_ACCFULL + 2 * s + reg));
-            if (iss_blk + 1 == nb) {
-                // The tile's A stage is free once its MMAs are done.  A commit only tracks the MMAs of the committing thread, and
-                // the tile's earlier blocks were issued by the other warps: all but the previous one have already been consumed,
-                // so wait for that one's completion and then commit for this block.
-                if (iss_use > 0) mbar_wait(bar(B_ACCFULL + 2 * s + (reg ^ 1u)), ((iss_use - 1) >> 1) & 1u);
-                tc_commit(bar(B_AEMPTY + iss_stage));
+            ++q.use;
+            if (++q.blk == nb) {
+                tc_commit(bar(B_AEMPTY + q.stage));      // every MMA that read this A stage came from this thread: one commit covers them
+                q.blk = 0;
+                q.tile += 2LL * gridDim.x;
+                // the stream's next tile is two further on in the CTA's sequence
+                q.i += 2;
+                q.stage = q.i % MMA_A_STAGES;
+                q.phase = (q.i / MMA_A_STAGES) & 1u;
             }
-            }
-            ++iss_use;
-            if (++iss_blk == nb) {
-                iss_blk = 0;
-                iss_tile += 2LL * gridDim.x;
-                // the stream's next tile is two further on in the CTA's sequence: stage (i + 2) % 3, and the phase of that
-                // stage's barrier flips every third tile
-                iss_i += 2;
-                iss_stage = iss_i % MMA_A_STAGES;
-                iss_phase = (iss_i / MMA_A_STAGES) & 1u;
-            }
+            return true;
         };
-        issue_next(quarter == 0);
-        issue_next(quarter == 1);
-        __syncwarp();
+        long long idle_since = 0;
+        unsigned idle = 0;
+        while (st[0].tile < n_tiles || st[1].tile < n_tiles) {
+            bool any = false;
+#pragma unroll
+            for (int s = 0; s < 2; ++s)
+                if (st[s].tile < n_tiles) any = try_issue(st[s], s) || any;
+            if (any) { idle = 0; idle_since = 0; continue; }
+#if HFE_ISSUE_MODE == 1
+            __nanosleep(32);
+#elif HFE_ISSUE_MODE == 2
+            {   // block (hardware-suspended try_wait) on what the stream that is further behind needs next
+                const int s = (st[1].tile < n_tiles && (st[0].tile >= n_tiles || st[1].use < st[0].use)) ? 1 : 0;
+                const IssueState& q = s ? st[1] : st[0];
+                if (q.use >= 2) mbar_wait(bar(B_ACCEMPTY + 2 * s + (q.use & 1u)), ((q.use >> 1) - 1u) & 1u);
+            }
+#endif
+            if ((++idle & 0xFFFFu) == 0) {               // about a second without progress can only be a protocol bug
+                if (idle_since == 0) idle_since = clock64();
+                else if (clock64() - idle_since > 4000000000LL) __trap();
+            }
+        }
+        }
+    } else {
+        // =========================== exponent warps ================================================================================
+        set_max_regs<MMA_REGS[2], MMA_REGS[2] >= 96>();
+        const int s = (warp - MMA_EPI_WARP0) >> 2;                   // stream
+        const int row_in_tile = (warp & 3) * 32 + lane;              // TMEM lane = row of the tile (warp % 4 picks the lane quarter)
+        const unsigned lane_base = tmem_base + ((unsigned)((warp & 3) * 32) << 16);
+        mbar_wait(bar(B_W), 0);
+        const float* s_coef = reinterpret_cast<const float*>(s_w + (size_t)nb * bsv * (MMA_B_CHUNKS * 16));
+        const int steps = bsv >> 4;
 #ifdef HFE_MMA_TRACE
         const long long t_loop0 = clock64();
 #endif
@@ -497,7 +560,7 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
                 // partial sums of 4 vectors each folded into the float64 accumulator; the TMEM load of the next step is in
                 // flight while this one is consumed
                 unsigned va[16], vb[16];
-                auto consume = [&](const unsigned (&v)[16], const float4* cp) {
+                auto consume = [&](const unsigned (&v)[16], const float4* cp) -> float {
                     float2 a0 = make_float2(0.f, 0.f), a1 = a0;
 #pragma unroll
                     for (int k = 0; k < 4; ++k) {
@@ -507,7 +570,7 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
                         a0 = __ffma2_rn(e0, make_float2(c.x, c.y), a0);
                         a1 = __ffma2_rn(e1, make_float2(c.z, c.w), a1);
                     }
-                    two_sum_add(acc_hi, acc_lo, (a0.x + a0.y) + (a1.x + a1.y));
+                    return (a0.x + a0.y) + (a1.x + a1.y);
                 };
                 tmem_ld16(taddr, va);
                 int st = 0;
@@ -515,28 +578,24 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
                 for (; st + 2 <= steps; st += 2) {
                     tmem_ld_wait(va);
                     tmem_ld16(taddr + (st + 1) * 16, vb);
-                    consume(va, coef4 + st * 4);
+                    const float pa = consume(va, coef4 + st * 4);
                     tmem_ld_wait(vb);
                     if (st + 2 < steps) tmem_ld16(taddr + (st + 2) * 16, va);
-                    consume(vb, coef4 + (st + 1) * 4);
+                    const float pb = consume(vb, coef4 + (st + 1) * 4);
+                    two_sum_add(acc_hi, acc_lo, pa + pb);            // one error-free fold per 32 support vectors
                 }
                 if (st < steps) {
                     tmem_ld_wait(va);
-                    consume(va, coef4 + st * 4);
+                    two_sum_add(acc_hi, acc_lo, consume(va, coef4 + st * 4));
                     lin_dot = va[15];
                 } else {
                     lin_dot = vb[15];
                 }
-                // this region may be overwritten: once all four warps have said so, the issuer refills it with the block two ahead
+                // this region may be overwritten: once all four warps have said so, the issuing warp refills it with the block
+                // two ahead
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(bar(B_ACCEMPTY + 2 * s + reg));
-                {
-                    const bool mine = ((unsigned)(use + 2) & 3u) == quarter;
-                    if (mine) MMA_TRACE_WAIT(9, mbar_wait(bar(B_ACCEMPTY + 2 * s + reg), (unsigned)((use >> 1) & 1)));
-                    MMA_TRACE_WAIT(10, issue_next(mine));
-                }
-                __syncwarp();
             }
             // hand the row's sum to the producer thread that finishes it
             ring_sum((int)(i % MMA_RING))[row_in_tile] = widen_f32(acc_hi) + widen_f32(acc_lo);
