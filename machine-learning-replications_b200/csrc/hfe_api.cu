@@ -428,6 +428,7 @@ int hfe_abi_version(void) { return 2; }
 const char* hfe_last_error_string(void) { return g_last_error.c_str(); }
 
 int hfe_model_create(const void* blob, size_t blob_bytes, int device, hfe_model** out_model) {
+    try {
     if (!blob || !out_model) return fail(HFE_ERR_INVALID_ARGUMENT, "null blob or output pointer");
     *out_model = nullptr;
     if (device < 0) return fail(HFE_ERR_INVALID_ARGUMENT, "negative device ordinal");
@@ -479,13 +480,20 @@ int hfe_model_create(const void* blob, size_t blob_bytes, int device, hfe_model*
     }
     *out_model = h;
     return HFE_OK;
+    } catch (const std::exception& e) {       // nothing may unwind through the C boundary
+        return fail(HFE_ERR_INVALID_ARGUMENT, std::string("out of host memory or internal error: ") + e.what());
+    }
 }
 
 int hfe_model_calibrate_guards(hfe_model* model, double formula_scale) {
+    try {
     if (!model) return fail(HFE_ERR_INVALID_ARGUMENT, "null model");
     if (!(formula_scale > 0.0) || !(formula_scale <= 1e12)) return fail(HFE_ERR_INVALID_ARGUMENT, "formula_scale must be positive and finite");
     model->impl->guard_scale = formula_scale;
     return probe_guards(model);
+    } catch (const std::exception& e) {       // nothing may unwind through the C boundary
+        return fail(HFE_ERR_INVALID_ARGUMENT, std::string("out of host memory or internal error: ") + e.what());
+    }
 }
 
 void hfe_model_destroy(hfe_model* model) {
@@ -531,6 +539,7 @@ int hfe_model_set_tree_engine(hfe_model* model, int engine) {
 }
 
 int hfe_model_plan(const void* blob, size_t blob_bytes, hfe_model_info* out_info, int32_t* feature_order) {
+    try {
     if (!blob || !out_info) return fail(HFE_ERR_INVALID_ARGUMENT, "null blob or info pointer");
     std::vector<uint64_t> copy((blob_bytes + 7) / 8 + 1, 0);
     std::memcpy(copy.data(), blob, blob_bytes);
@@ -542,6 +551,9 @@ int hfe_model_plan(const void* blob, size_t blob_bytes, hfe_model_info* out_info
         for (int f = 0; f < F; ++f) feature_order[f] = impl->col_of[f];
     delete impl;
     return HFE_OK;
+    } catch (const std::exception& e) {       // nothing may unwind through the C boundary
+        return fail(HFE_ERR_INVALID_ARGUMENT, std::string("out of host memory or internal error: ") + e.what());
+    }
 }
 
 static void fill_info(const Model* m, hfe_model_info* info) {
@@ -919,6 +931,7 @@ extern "C" {
 
 int hfe_predict_host(const hfe_model* model, const double* x_rowmajor, int64_t n, double* proba_n2, uint8_t* labels,
                      double* decision, double* meta) {
+    try {
     if (!model || !model->impl) return fail(HFE_ERR_INVALID_ARGUMENT, "null model handle");
     if (n < 0) return fail(HFE_ERR_INVALID_ARGUMENT, "negative row count");
     if (n == 0) return HFE_OK;
@@ -1025,6 +1038,9 @@ int hfe_predict_host(const hfe_model* model, const double* x_rowmajor, int64_t n
         }
     }
     return HFE_OK;
+    } catch (const std::exception& e) {       // nothing may unwind through the C boundary
+        return fail(HFE_ERR_INVALID_ARGUMENT, std::string("out of host memory or internal error: ") + e.what());
+    }
 }
 
 }  // extern "C"
