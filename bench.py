@@ -310,12 +310,16 @@ def e2e_legs(ctx, clf, x, out, n, args):
         proba = clf.predict_proba(X64)
     dt = ctx.reduce((time.perf_counter() - t0) / steps, "max")
     diff = float(np.abs(proba[:, 1] - out[:rows, 1].cpu().numpy().astype(np.float64)).max())
-    res["e2e"] = {"value": rows * ctx.world / dt, "unit": "rows/s", "h2d_bytes_per_step": rows * 17 * 4,
+    # the library sends a chunk as bytes when all its values are integers in [0, 255] (lossless), else as float32
+    as_bytes = bool(((X64 == np.rint(X64)) & (X64 >= 0) & (X64 <= 255)).all())
+    res["e2e"] = {"value": rows * ctx.world / dt, "unit": "rows/s", "h2d_bytes_per_step": rows * 17 * (1 if as_bytes else 4),
+                  "wire_format": "uint8 (every value an integer in [0, 255]: lossless)" if as_bytes else "float32",
                   "d2h_bytes_per_step": rows * 2 * 4, "rows_per_step": rows, "steps": steps,
                   "host_input_bytes_per_step": rows * 17 * 8, "host_output_bytes_per_step": rows * 2 * 8,
                   "api": "HFStackB200.predict_proba(X): X numpy float64 [rows,17] C-order in pageable memory -> numpy "
-                         "float64 [rows,2]; hfe_predict_host narrows to float32 on host threads into pinned chunks "
-                         "(what crosses PCIe), 3 chunks in flight over 3 streams, ingest + scoring + D2H per chunk",
+                         "float64 [rows,2]; hfe_predict_host narrows on host threads into pinned chunks (bytes when the "
+                         "chunk is an integer cohort, else float32: what crosses PCIe), 3 chunks in flight over 3 streams, "
+                         "ingest + scoring + D2H per chunk",
                   "max_abs_diff_vs_device_path": diff}
     del X64, proba
     # (2) the same device path fed from pinned float32 / uint8 tensors (no host-side narrowing)

@@ -881,16 +881,13 @@ int predict_host_pipelined(const hfe_model* model, const double* x_rowmajor, int
     };
 
     int k = 0;
+    bool bytes_ok = true;
     for (int64_t begin = 0; begin < n; begin += C, ++k) {
         HostSlot& s = hp.slot[k % HOST_SLOTS];
         int rc = retire(s);
         if (rc) return rc;
         const int64_t rows = std::min(C, n - begin);
         const double* src = x_rowmajor + begin * F;
-        hp.pool->run([&](int t, int T) {
-            const int64_t e0 = rows * F * t / T, e1 = rows * F * (t + 1) / T;
-            narrow_rows(src + e0, s.h_in + e0, (size_t)(e1 - e0));
-        });
         float* d_raw = reinterpret_cast<float*>(s.d_buf + hp.off_raw);
         float* d_col = reinterpret_cast<float*>(s.d_buf + hp.off_col);
         float* d_out = reinterpret_cast<float*>(s.d_buf + hp.off_out);
@@ -898,8 +895,33 @@ int predict_host_pipelined(const hfe_model* model, const double* x_rowmajor, int
         double* d_dec = decision ? reinterpret_cast<double*>(s.d_buf + hp.off_dec) : nullptr;
         double* d_meta = meta ? reinterpret_cast<double*>(s.d_buf + hp.off_meta) : nullptr;
         uint32_t* d_status = reinterpret_cast<uint32_t*>(s.d_buf + hp.off_status);     // [ingest header | scoring status]
-        HFE_CUDA_TRY(cudaMemcpyAsync(d_raw, s.h_in, (size_t)rows * F * sizeof(float), cudaMemcpyHostToDevice, s.stream));
-        rc = hfe_ingest_rowmajor_f32(d_raw, rows, F, d_col, C, d_status, s.stream);
+        // Wire format, chosen per chunk: while every value so far in this call was an integer in [0, 255] (cohort variables
+        // are counts, classes and yes/no answers) the chunk crosses PCIe as bytes -- 17 instead of 68 per row, lossless, so
+        // the scores are the same bits; the first chunk that holds anything else is narrowed again to float32 and the rest
+        // of the call does not try bytes any more.
+        bool as_bytes = bytes_ok;
+        if (as_bytes) {
+            std::atomic<int> failed{0};
+            unsigned char* h_u8 = reinterpret_cast<unsigned char*>(s.h_in);
+            hp.pool->run([&](int t, int T) {
+                // thread shares start on 16-byte boundaries of the destination so that the streaming stores stay aligned
+                const int64_t total = rows * F;
+                const int64_t e0 = (total * t / T) & ~(int64_t)15, e1 = t + 1 == T ? total : (total * (t + 1) / T) & ~(int64_t)15;
+                if (e1 > e0 && !narrow_rows_u8(src + e0, h_u8 + e0, (size_t)(e1 - e0))) failed.store(1, std::memory_order_relaxed);
+            });
+            if (failed.load()) { as_bytes = false; bytes_ok = false; }
+        }
+        if (as_bytes) {
+            HFE_CUDA_TRY(cudaMemcpyAsync(d_raw, s.h_in, (size_t)rows * F, cudaMemcpyHostToDevice, s.stream));
+            rc = hfe_ingest_rowmajor_u8(reinterpret_cast<const uint8_t*>(d_raw), rows, F, d_col, C, d_status, s.stream);
+        } else {
+            hp.pool->run([&](int t, int T) {
+                const int64_t e0 = rows * F * t / T, e1 = rows * F * (t + 1) / T;
+                narrow_rows(src + e0, s.h_in + e0, (size_t)(e1 - e0));
+            });
+            HFE_CUDA_TRY(cudaMemcpyAsync(d_raw, s.h_in, (size_t)rows * F * sizeof(float), cudaMemcpyHostToDevice, s.stream));
+            rc = hfe_ingest_rowmajor_f32(d_raw, rows, F, d_col, C, d_status, s.stream);
+        }
         if (rc) return rc;
         rc = score_common(model, d_col, rows, C, -1, nullptr, d_out, nullptr, d_lab, d_dec, d_meta, nullptr, nullptr,
                           d_status + HFE_STATUS_HEADER_WORDS, s.stream, all_f64);

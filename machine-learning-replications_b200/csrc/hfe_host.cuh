@@ -226,6 +226,55 @@ inline bool host_has_avx2() {
 }
 #endif
 
+// float64 -> uint8 where that loses nothing (cohort variables are small non-negative integers): returns false at the first
+// value that is not an integer in [0, 255] -- NaN included -- and the chunk is then narrowed to float32 instead.
+inline bool narrow_rows_u8_plain(const double* __restrict__ src, unsigned char* __restrict__ dst, size_t count) {
+    for (size_t i = 0; i < count; ++i) {
+        const double v = src[i];
+        const int q = (v >= 0.0 && v <= 255.0) ? (int)v : -1;
+        if (q < 0 || (double)q != v) return false;
+        dst[i] = (unsigned char)q;
+    }
+    return true;
+}
+
+#if defined(__x86_64__)
+__attribute__((target("avx2"))) inline bool narrow_rows_u8_avx2(const double* __restrict__ src, unsigned char* __restrict__ dst, size_t count) {
+    size_t i = 0;
+    while (i < count && (reinterpret_cast<uintptr_t>(dst + i) & 15)) {
+        if (!narrow_rows_u8_plain(src + i, dst + i, 1)) return false;
+        ++i;
+    }
+    const __m128i pick = _mm_setr_epi8(0, 4, 8, 12, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1);
+    __m256d bad = _mm256_setzero_pd();
+    __m128i high = _mm_setzero_si128();
+    for (; i + 16 <= count; i += 16) {
+        __m128i out = _mm_setzero_si128();
+        __m128i part[4];
+        for (int k = 0; k < 4; ++k) {
+            const __m256d v = _mm256_loadu_pd(src + i + 4 * k);
+            const __m128i q = _mm256_cvttpd_epi32(v);                              // NaN / out of range -> 0x80000000
+            bad = _mm256_or_pd(bad, _mm256_cmp_pd(_mm256_cvtepi32_pd(q), v, _CMP_NEQ_UQ));
+            high = _mm_or_si128(high, q);                                           // any bit above the low byte (or the sign) set?
+            part[k] = _mm_shuffle_epi8(q, pick);                                    // the four low bytes, in the low dword
+        }
+        out = _mm_unpacklo_epi64(_mm_unpacklo_epi32(part[0], part[1]), _mm_unpacklo_epi32(part[2], part[3]));
+        _mm_stream_si128(reinterpret_cast<__m128i*>(dst + i), out);
+    }
+    _mm_sfence();
+    if (_mm256_movemask_pd(bad) != 0) return false;
+    if (!_mm_testz_si128(high, _mm_set1_epi32(~0xFF))) return false;
+    return narrow_rows_u8_plain(src + i, dst + i, count - i);
+}
+#endif
+
+inline bool narrow_rows_u8(const double* src, unsigned char* dst, size_t count) {
+#if defined(__x86_64__)
+    if (host_has_avx2()) return narrow_rows_u8_avx2(src, dst, count);
+#endif
+    return narrow_rows_u8_plain(src, dst, count);
+}
+
 inline void narrow_rows(const double* src, float* dst, size_t count) {
 #if defined(__x86_64__)
     if (host_has_avx2()) { narrow_rows_avx2(src, dst, count); return; }

@@ -265,6 +265,18 @@ def test_large_host_batches_take_the_chunk_pipeline(case, clf_for, pkg, torch_cu
     with pytest.raises(ValueError):
         clf.predict_proba(bad)
     assert np.array_equal(clf.predict_proba(X[:70_000]), proba[:70_000])      # the pipeline is reusable after an error
+    # wire format: integer cohorts (like X) cross PCIe as bytes; the first chunk holding anything that is not an integer
+    # in [0, 255] -- here in the second chunk, after the first went as bytes -- switches the call to float32.  Same bits.
+    assert float(np.abs(X - np.rint(X)).max()) == 0.0 and X.min() >= 0 and X.max() <= 255
+    for value in (0.5, -1.0, 256.0, 1e9, 254.999999999, -0.0):
+        X2 = X.copy()
+        X2[(1 << 18) + 12_345, 3] = value
+        X2[n - 1, 16] = value
+        want, _ = device_scores(clf, X2)
+        assert np.array_equal(clf.predict_proba(X2)[:, 1], want[:, 1]), value
+    X2[(1 << 18) + 5, 0] = np.nan
+    with pytest.raises(ValueError):
+        clf.predict_proba(X2)
 
 
 def test_permuted_column_pass_and_score_count(published, clf_for, pkg, torch_cuda):
