@@ -231,12 +231,11 @@ class HFStackB200:
         capi.check(self._lib.hfe_predict_proba(self._handle, x.data_ptr(), n, x.stride(0), out.data_ptr(),
                                                status.data_ptr(), self._stream()))
         self.last_status = status
-        # one word of the status header, snapshotted behind the call on the same stream: what check() / the next
-        # device call look at (the caller may reuse ``status`` for another call in the meantime)
+        # an event behind the call: check() / the next device call look at the call's error bits once it has passed
+        # (at the status array the caller gave -- a caller who reuses it for another call sees that call's bits)
         if getattr(self, "_pending", None) is None:
-            self._pending = (torch.zeros(1, dtype=torch.int32, device=x.device), torch.cuda.Event())
-        self._pending[0].copy_(status[:1], non_blocking=True)
-        self._pending[1].record(torch.cuda.current_stream(self.device))
+            self._pending = torch.cuda.Event()
+        self._pending.record(torch.cuda.current_stream(self.device))
         self._pending_live = True
         return out
 
@@ -253,9 +252,9 @@ class HFStackB200:
         """If the previous ``predict_proba_device`` call has finished, look at its error bits (no waiting).  A work-list
         overflow of that call is reported as a ``RuntimeWarning`` here -- the caller never asked about it, and its
         non-finite rows are visible as NaN outputs anyway; ``check()`` raises."""
-        if getattr(self, "_pending_live", False) and self._pending[1].query():
+        if getattr(self, "_pending_live", False) and self._pending.query():
             self._pending_live = False
-            if int(self._pending[0].item()) & capi.WORKLIST_OVERFLOW:
+            if int(self.last_status[0].item()) & capi.WORKLIST_OVERFLOW:
                 import warnings
                 warnings.warn("the previous predict_proba_device call overflowed its work list: rows beyond "
                               "WORKLIST_CAPACITY kept their float32-path result; rerun that batch through "
@@ -269,9 +268,9 @@ class HFStackB200:
         torch.cuda.current_stream(self.device).synchronize()
         if status is not None:
             self._raise_for_flags(int(status[0].item()))
-        elif getattr(self, "_pending", None) is not None:
+        elif getattr(self, "last_status", None) is not None:
             self._pending_live = False
-            self._raise_for_flags(int(self._pending[0].item()))
+            self._raise_for_flags(int(self.last_status[0].item()))
 
     def score_device(self, x, n=None, perm_col=-1, perm_idx=None, out=None, labels=None, decision=None, meta=None,
                      y=None, score=None, status=None):
