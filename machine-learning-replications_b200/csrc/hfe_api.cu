@@ -145,7 +145,7 @@ template <int TM>
 int launch_mma(const Model* m, const ScoreParams& P, cudaStream_t stream) {
     const MmaParams& Q = m->mma;
     const size_t smem = (((size_t)Q.w_bytes + 1023) & ~(size_t)1023) + (size_t)MMA_A_STAGES * MMA_A_STAGE_BYTES +
-                        (size_t)MMA_RING * MMA_RING_SLOT_BYTES + 48 * sizeof(unsigned long long) + 128;
+                        (size_t)MMA_RING * MMA_RING_SLOT_BYTES + MMA_BARRIERS * sizeof(unsigned long long) + 128;
     auto kernel = hfe_mma_kernel<TM>;
     static std::mutex mu;
     static std::map<int, int> ready;

@@ -66,7 +66,7 @@ constexpr int MMA_A_CHUNKS = 12;                         // 16-byte K chunks per
 constexpr int MMA_A_STAGE_BYTES = (MMA_TILE_ROWS / 8) * MMA_A_CHUNKS * 128;                   // 24 576
 constexpr int MMA_RING = 12;                             // tiles between a row's production and its float64 epilogue
 constexpr int MMA_RING_SLOT_BYTES = MMA_TILE_ROWS * 20;  // per tile and row: RBF sum (f64), logistic dot, stump score, gamma|z|^2 (f32)
-constexpr int MMA_REGION_COLS = 128;                     // TMEM columns per region
+// MMA_REGIONS / MMA_REGION_COLS (hfe_model.cuh): TMEM regions per stream and their width
 static_assert(MMA_A_STAGES * MMA_A_STAGE_BYTES == 5 * 24576 && MMA_RING * MMA_RING_SLOT_BYTES == 12 * 2560,
               "hfe_model.cuh sizes the support-vector limit of this kernel from these");
 constexpr int MMA_TAIL_ROWS = 4;                         // tiles whose float64 epilogue one thread runs interleaved
@@ -199,10 +199,10 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
     unsigned char* s_a = smem + w_region;
     unsigned char* s_ring = s_a + MMA_A_STAGES * MMA_A_STAGE_BYTES;
     unsigned long long* s_bar = reinterpret_cast<unsigned long long*>(s_ring + MMA_RING * MMA_RING_SLOT_BYTES);
-    unsigned* s_misc = reinterpret_cast<unsigned*>(s_bar + 48);
-    enum { B_W = 0, B_AFULL = 1, B_AEMPTY = B_AFULL + MMA_A_STAGES, B_ACCFULL = B_AEMPTY + MMA_A_STAGES, B_ACCEMPTY = B_ACCFULL + 4,
-           B_SUMFULL = B_ACCEMPTY + 4, B_RINGFREE = B_SUMFULL + MMA_RING, B_COUNT = B_RINGFREE + MMA_RING };
-    static_assert(B_COUNT <= 48, "barrier block");
+    unsigned* s_misc = reinterpret_cast<unsigned*>(s_bar + MMA_BARRIERS);
+    enum { B_W = 0, B_AFULL = 1, B_AEMPTY = B_AFULL + MMA_A_STAGES, B_ACCFULL = B_AEMPTY + MMA_A_STAGES, B_ACCEMPTY = B_ACCFULL + 2 * MMA_REGIONS,
+           B_SUMFULL = B_ACCEMPTY + 2 * MMA_REGIONS, B_RINGFREE = B_SUMFULL + MMA_RING, B_COUNT = B_RINGFREE + MMA_RING };
+    static_assert(B_COUNT <= MMA_BARRIERS, "barrier block");
     auto bar = [&](int i) { return smem_addr(s_bar + i); };
     auto ring_sum = [&](int slot) { return reinterpret_cast<double*>(s_ring + slot * MMA_RING_SLOT_BYTES); };
     auto ring_lin = [&](int slot) { return reinterpret_cast<float*>(s_ring + slot * MMA_RING_SLOT_BYTES + MMA_TILE_ROWS * 8); };
@@ -224,7 +224,7 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
     if (tid == 0) {
         mbar_init(bar(B_W), 1);
         for (int i = 0; i < MMA_A_STAGES; ++i) { mbar_init(bar(B_AFULL + i), 4); mbar_init(bar(B_AEMPTY + i), 1); }
-        for (int i = 0; i < 4; ++i) { mbar_init(bar(B_ACCFULL + i), 1); mbar_init(bar(B_ACCEMPTY + i), 4); }
+        for (int i = 0; i < 2 * MMA_REGIONS; ++i) { mbar_init(bar(B_ACCFULL + i), 1); mbar_init(bar(B_ACCEMPTY + i), 4); }
         for (int i = 0; i < MMA_RING; ++i) { mbar_init(bar(B_SUMFULL + i), 4); mbar_init(bar(B_RINGFREE + i), MMA_FINISH_WARPS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -467,15 +467,15 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
             st[s].ext = false;
         }
         auto try_issue = [&](IssueState& q, const int s) -> bool {
-            const unsigned reg = q.use & 1u;
+            const unsigned reg = q.use % MMA_REGIONS;
             // the region must have been drained (block use - 2) and, for the first block of a tile, the A stage filled
-            if (q.use >= 2 && !mbar_test(bar(B_ACCEMPTY + 2 * s + reg), ((q.use >> 1) - 1u) & 1u)) return false;
+            if (q.use >= MMA_REGIONS && !mbar_test(bar(B_ACCEMPTY + MMA_REGIONS * s + reg), ((q.use / MMA_REGIONS) - 1u) & 1u)) return false;
             if (q.blk == 0) {
                 if (!mbar_test(bar(B_AFULL + q.stage), q.phase)) return false;
                 q.ext = (s_ext[q.stage * 4 + 0] | s_ext[q.stage * 4 + 1] | s_ext[q.stage * 4 + 2] | s_ext[q.stage * 4 + 3]) != 0;
             }
             tc_fence_after();
-            const unsigned d = tmem_base + (2u * s + reg) * MMA_REGION_COLS;
+            const unsigned d = tmem_base + ((unsigned)MMA_REGIONS * s + reg) * MMA_REGION_COLS;
             const unsigned long long a0 = a_desc0 + q.stage * (MMA_A_STAGE_BYTES / 16);
             const unsigned long long b0 = b_desc0 + (unsigned)q.blk * b_blk_units;
             // a K-step takes two adjacent 16-byte chunks of each operand (chunks are 128 bytes = 8 descriptor units apart).
@@ -496,7 +496,7 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
             umma_bf16(d, a0 + 2 * 8, b0 + 5 * 8, idesc, 1u);                  // (H2 0).(WM2 .)
             umma_bf16(d, a0 + 0 * 8, b0 + 6 * 8, idesc, 1u);                  // (H0 H1).(WH0 WH1)        1
             umma_bf16(d, a0 + 2 * 8, b0 + 8 * 8, idesc, 1u);                  // (H2 0).(WH2 .)
-            tc_commit(bar(B_ACCFULL + 2 * s + reg));
+            tc_commit(bar(B_ACCFULL + MMA_REGIONS * s + reg));
             ++q.use;
             if (++q.blk == nb) {
                 tc_commit(bar(B_AEMPTY + q.stage));      // every MMA that read this A stage came from this thread: one commit covers them
@@ -523,7 +523,7 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
             {   // block (hardware-suspended try_wait) on what the stream that is further behind needs next
                 const int s = (st[1].tile < n_tiles && (st[0].tile >= n_tiles || st[1].use < st[0].use)) ? 1 : 0;
                 const IssueState& q = s ? st[1] : st[0];
-                if (q.use >= 2) mbar_wait(bar(B_ACCEMPTY + 2 * s + (q.use & 1u)), ((q.use >> 1) - 1u) & 1u);
+                if (q.use >= MMA_REGIONS) mbar_wait(bar(B_ACCEMPTY + MMA_REGIONS * s + (q.use % MMA_REGIONS)), ((q.use / MMA_REGIONS) - 1u) & 1u);
             }
 #endif
             if ((++idle & 0xFFFFu) == 0) {               // about a second without progress can only be a protocol bug
@@ -551,10 +551,10 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
 #pragma unroll 1
             for (int blk = 0; blk < nb; ++blk) {
                 const long long use = j * nb + blk;                  // this stream's running count of blocks
-                const int reg = (int)(use & 1);
-                MMA_TRACE_WAIT(blk < 7 ? blk : 7, mbar_wait(bar(B_ACCFULL + 2 * s + reg), (unsigned)((use >> 1) & 1)));
+                const int reg = (int)(use % MMA_REGIONS);
+                MMA_TRACE_WAIT(blk < 7 ? blk : 7, mbar_wait(bar(B_ACCFULL + MMA_REGIONS * s + reg), (unsigned)((use / MMA_REGIONS) & 1)));
                 tc_fence_after();
-                const unsigned taddr = lane_base + (unsigned)((2 * s + reg) * MMA_REGION_COLS);
+                const unsigned taddr = lane_base + (unsigned)((MMA_REGIONS * s + reg) * MMA_REGION_COLS);
                 const float4* coef4 = reinterpret_cast<const float4*>(s_coef + blk * bsv);
                 // 16 support vectors per step: 2^T on the MUFU pipe, coefficient FFMA2 (two vectors per instruction), float32
                 // partial sums of 4 vectors each folded into the float64 accumulator; the TMEM load of the next step is in
@@ -595,7 +595,7 @@ hfe_mma_kernel(const __grid_constant__ ScoreParams P, const __grid_constant__ Mm
                 // two ahead
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(bar(B_ACCEMPTY + 2 * s + reg));
+                if (lane == 0) mbar_arrive(bar(B_ACCEMPTY + MMA_REGIONS * s + reg));
             }
             // hand the row's sum to the producer thread that finishes it
             ring_sum((int)(i % MMA_RING))[row_in_tile] = widen_f32(acc_hi) + widen_f32(acc_lo);

@@ -128,7 +128,13 @@ struct ScoreParams {
 };
 
 // Tensor-core path of the RBF sum (hfe_mma.cuh): the B operand image and what the producers need to build the A operand.
-constexpr int MMA_MAX_SV = 512;       // 4 blocks of up to 128 support vectors = the 512 TMEM columns (4 regions in flight)
+constexpr int MMA_MAX_SV = 512;       // the 512 TMEM columns hold the blocks in flight
+#ifndef HFE_MMA_REGIONS
+#define HFE_MMA_REGIONS 2             // TMEM regions per stream: 2 x 128 columns (1.55 ms) or 4 x 64 (1.72 ms: the per-block bookkeeping outweighs the deeper pipeline)
+#endif
+constexpr int MMA_REGIONS = HFE_MMA_REGIONS;             // blocks of a stream that can be in TMEM at once
+constexpr int MMA_REGION_COLS = 256 / MMA_REGIONS;       // TMEM columns per region = the largest block of support vectors
+constexpr int MMA_BARRIERS = 56;                         // mbarrier slots in shared memory
 constexpr int MMA_B_CHUNKS = 10;      // 16-byte K chunks per support vector: WL0 WL1 WL2 WM0 WM1 WM2 WH0 WH1 WH2 0
 
 struct MmaParams {
@@ -558,7 +564,7 @@ inline int build_svc(Model* m, const ParsedBlob& pb, uint32_t idx) {
         };
         auto bf16_val = [](uint16_t h) { uint32_t b = (uint32_t)h << 16; float v; std::memcpy(&v, &b, 4); return v; };
         const int n_cols = n_sv + 1;                        // the last column carries the logistic member's dot product
-        const int nb = (n_cols + 127) / 128, per_block = (n_cols + nb - 1) / nb;
+        const int nb = (n_cols + MMA_REGION_COLS - 1) / MMA_REGION_COLS, per_block = (n_cols + nb - 1) / nb;
         const int bsv = ((per_block + 15) / 16) * 16, n_pad = nb * bsv;
         const size_t img_bytes = (size_t)n_pad * MMA_B_CHUNKS * 16;
         mma_img.assign(img_bytes + (size_t)n_pad * sizeof(float), 0);
@@ -597,7 +603,7 @@ inline int build_svc(Model* m, const ParsedBlob& pb, uint32_t idx) {
             coef_tab[col] = (float)folded;
         }
         // [B image + coefficients | 5 A stages | 12 ring slots | barriers] must fit one block's 227 KB (hfe_mma.cuh)
-        usable = usable && ((mma_img.size() + 1023) & ~(size_t)1023) + 5 * 24576 + 12 * 2560 + 512 <= 227 * 1024;
+        usable = usable && ((mma_img.size() + 1023) & ~(size_t)1023) + 5 * 24576 + 12 * 2560 + MMA_BARRIERS * 8 + 128 <= 227 * 1024;
         if (usable) {
             Q.nb = nb;
             Q.block_sv = bsv;
