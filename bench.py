@@ -347,6 +347,22 @@ def e2e_legs(ctx, clf, x, out, n, args):
                     "h2d_gb_per_s_per_gpu": rows * bpr / dt / 1e9,
                     "api": "HFStackB200.predict_proba_pinned (pinned rows in, pinned probabilities out)",
                     "max_abs_diff_vs_device_path": float((out_host[:4096].to(ctx.dev) - out[:4096]).abs().max().item())}
+    # the host link by itself: every rank copies the same pinned float32 rows host -> device at the same time, nothing else
+    # running -- the ceiling any end-to-end figure at this GPU count is to be read against
+    dst = torch.empty_like(x_host, device=ctx.dev)
+    dst.copy_(x_host, non_blocking=True)
+    torch.cuda.synchronize()
+    ctx.barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        dst.copy_(x_host, non_blocking=True)
+    torch.cuda.synchronize()
+    dt = ctx.reduce((time.perf_counter() - t0) / steps, "max")
+    res["host_link"] = {"plain_h2d_gb_per_s_per_gpu": x_host.numel() * 4 / dt / 1e9,
+                        "plain_h2d_gb_per_s_all_gpus": x_host.numel() * 4 * ctx.world / dt / 1e9,
+                        "host_cpus": len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else None,
+                        "note": "concurrent cudaMemcpyAsync of 680 MB pinned float32 per rank; host_cpus = CPUs this rank is bound to"}
+    del dst
     res["e2e_u8_cohort"]["lossless"] = lossless
     res["e2e_u8_cohort"]["note"] = ("the cohort held as uint8 (every schema variable is a small non-negative integer); "
                                     "not the headline: the reference takes float arrays")
@@ -533,6 +549,7 @@ def run_ours(args):
         "e2e": e2e["e2e"],
         "e2e_pinned_f32": e2e["e2e_pinned_f32"],
         "e2e_u8_cohort": e2e["e2e_u8_cohort"],
+        "host_link": e2e["host_link"],
         "gpu_launches": 2 * args.steps * world,      # scoring pass + work-list fix-up per step and rank
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                      "frac": achieved / hbm_peak, "traffic": traffic, "traffic_from_profile": traffic_profile,
