@@ -153,6 +153,12 @@ int launch_mma(const Model* m, const ScoreParams& P, cudaStream_t stream) {
     {
         std::lock_guard<std::mutex> lock(mu);
         if (!ready.count(m->device)) {
+            // the warpgroups re-deal their registers with setmaxnreg; what they ask for in all must fit what the CTA is
+            // launched with, or the first setmaxnreg.inc would wait forever -- refuse instead
+            cudaFuncAttributes attr{};
+            HFE_CUDA_TRY(cudaFuncGetAttributes(&attr, kernel));
+            if (attr.numRegs * 5 < MMA_REGS[0] + MMA_REGS[1] + 2 * MMA_REGS[2] + MMA_REGS[3])
+                return fail(HFE_ERR_UNSUPPORTED, "tensor-core kernel was built with fewer registers per thread than its warpgroups re-deal");
             HFE_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
             ready[m->device] = 1;
         }
