@@ -163,6 +163,19 @@ int hfe_score_permuted(const hfe_model* model, const float* x, int64_t n, int64_
                        const int32_t* perm_idx, int64_t perm_stride, int32_t n_sel, const int32_t* sel,
                        const uint8_t* y, unsigned long long* scores, uint32_t* flags, uint32_t* status, void* stream);
 
+/* Permutation importance with scikit-learn's own index vectors, shuffles and scoring overlapped
+ * (SK/inspection/_permutation_importance.py:31-76, 278-313): job k scores the matrix with column job_col[k] read through
+ * the job_rep[k]-th index vector (job_col[k] < 0: unpermuted, the baseline) and scores[k] += #{labels == y}; flags[k] (may be
+ * NULL) receives that pass's status[0].  The vectors are what hfe_perm_indices(seed, n, .) returns; they are made on host
+ * threads while earlier passes run on the device -- vector r is written to perm_host + r*n (HOST int32 [n_repeats][n], kept
+ * for the caller), copied to perm_dev + r*n (DEVICE int32 [n_repeats][n]) and used as soon as it is complete -- so the
+ * jobs must be listed with ascending job_rep.  job_col / job_rep are HOST arrays.  Returns when everything is enqueued
+ * and the last vector is made. */
+int hfe_permutation_passes(const hfe_model* model, const float* x, int64_t n, int64_t ld, const uint8_t* y, uint32_t seed,
+                           int32_t n_repeats, int32_t n_jobs, const int32_t* job_col, const int32_t* job_rep,
+                           int32_t* perm_host, int32_t* perm_dev, unsigned long long* scores, uint32_t* flags,
+                           uint32_t* status, void* stream);
+
 /* The index vectors scikit-learn's permutation_importance uses for one column (same file, lines 66-74, 278): a
  * RandomState(seed) -- numpy's legacy MT19937 stream -- shuffles one index vector n_repeats times in a row and applies it
  * each time to the already permuted column; out[r*n + i] is the row whose value lands in row i at repeat r.  Host

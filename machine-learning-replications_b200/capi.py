@@ -21,7 +21,7 @@ METRIC_BINS = 65536
 
 EXPORTS = [
     "hfe_abi_version", "hfe_last_error_string", "hfe_model_calibrate_guards", "hfe_model_create", "hfe_model_destroy", "hfe_model_get_info", "hfe_model_plan", "hfe_model_set_rbf_engine", "hfe_model_set_tree_engine",
-    "hfe_predict_proba", "hfe_predict", "hfe_score", "hfe_score_permuted", "hfe_perm_indices", "hfe_apply", "hfe_predict_proba_f64", "hfe_score_f64", "hfe_synth_rows",
+    "hfe_predict_proba", "hfe_predict", "hfe_score", "hfe_score_permuted", "hfe_perm_indices", "hfe_permutation_passes", "hfe_apply", "hfe_predict_proba_f64", "hfe_score_f64", "hfe_synth_rows",
     "hfe_ingest_rowmajor_f64", "hfe_ingest_rowmajor_f32", "hfe_ingest_rowmajor_i64", "hfe_ingest_rowmajor_u8", "hfe_knn1_impute", "hfe_predict_host", "hfe_predict_proba_noalloc", "hfe_binary_metrics",
 ]
 
@@ -73,6 +73,7 @@ def load_library(path: str = LIB_PATH):
     lib.hfe_score.argtypes = [vp, vp, i64, i64, i32, vp, vp, vp, vp, vp, vp, vp, vp, vp]
     lib.hfe_score_permuted.argtypes = [vp, vp, i64, i64, i32, vp, i64, i32, vp, vp, vp, vp, vp, vp]
     lib.hfe_perm_indices.argtypes = [C.c_uint32, i64, i32, vp]
+    lib.hfe_permutation_passes.argtypes = [vp, vp, i64, i64, vp, C.c_uint32, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp]
     lib.hfe_apply.argtypes = [vp, vp, i64, i64, vp, vp]
     lib.hfe_predict_proba_f64.argtypes = [vp, vp, i64, i64, vp, vp, vp]
     lib.hfe_score_f64.argtypes = [vp, vp, i64, i64, vp, vp, vp, vp, vp, vp]

@@ -672,48 +672,165 @@ struct Mt19937 {
 };
 }  // namespace
 
-int hfe_perm_indices(uint32_t seed, int64_t n, int32_t n_repeats, int32_t* out) {
-    if (n < 0 || n > 0x7FFFFFFF || n_repeats < 0 || (!out && n > 0 && n_repeats > 0))
-        return fail(HFE_ERR_INVALID_ARGUMENT, "bad permutation request");
-    try {
-        Mt19937 rng(seed);
+namespace {
+// scikit-learn's index vectors for permutation importance (SK/inspection/_permutation_importance.py:66-74): RandomState(seed)
+// shuffles ONE index vector n_repeats times and applies it each time to the already permuted column, so the effective
+// source index composes: e_r = e_{r-1}[idx_r].  Three threads: one makes the draws (masked rejection on the MT19937 stream:
+// they do not depend on the array), the caller's applies the swaps -- a serial chain, fed a block ahead with its targets
+// prefetched -- and one composes a finished shuffle with the previous vector while the next shuffle proceeds.  `ready`
+// counts the vectors that are complete in `out`, in order.
+struct ShuffleJob {
+    uint32_t seed = 0;
+    int64_t n = 0;
+    int32_t reps = 0;
+    int32_t* out = nullptr;
+    std::atomic<int> ready{0};
+    std::atomic<int> failed{0};
+
+    static constexpr int BLK = 4096, NBLK = 8;
+
+    void run() {
+        try {
+            run_impl();
+        } catch (const std::exception&) {
+            failed.store(1);
+        }
+        if (failed.load()) ready.store(reps);          // never leave a waiter spinning
+    }
+
+private:
+    void run_impl() {
+        if (n <= 0 || reps <= 0) { ready.store(reps); return; }
+        std::vector<uint32_t> ring((size_t)BLK * NBLK);
+        std::atomic<uint64_t> produced{0}, consumed{0};
+        const uint64_t per_rep = (uint64_t)(n - 1), total = per_rep * (uint64_t)reps;
+        std::thread drawer([&] {
+            Mt19937 rng(seed);
+            uint64_t made = 0;
+            while (made < total) {
+                const uint64_t b = produced.load(std::memory_order_relaxed);
+                while (b - consumed.load(std::memory_order_acquire) >= (uint64_t)NBLK) std::this_thread::yield();
+                uint32_t* dst = &ring[(size_t)(b % NBLK) * BLK];
+                const int cnt = (int)std::min<uint64_t>(BLK, total - made);
+                for (int k = 0; k < cnt; ++k) {
+                    const uint32_t top = (uint32_t)(per_rep - (made + k) % per_rep);        // i runs n-1 .. 1 in every repeat
+                    const uint32_t mask = 0xFFFFFFFFu >> __builtin_clz(top);
+                    uint32_t jv;
+                    while ((jv = rng.next() & mask) > top) {}
+                    dst[k] = jv;
+                }
+                made += cnt;
+                produced.store(b + 1, std::memory_order_release);
+            }
+        });
         std::vector<int32_t> idx((size_t)n), snap[2];
         for (int64_t i = 0; i < n; ++i) idx[(size_t)i] = (int32_t)i;
         std::thread composer;
-        constexpr int AHEAD = 256;
-        uint32_t js[AHEAD];
-        for (int32_t r = 0; r < n_repeats; ++r) {
-            // RandomState.shuffle: for i = n-1 .. 1: j = random_interval(i) (masked rejection on 32-bit draws); swap.
-            // The draws do not depend on the array, so they are made a block ahead and their targets prefetched: the swap
-            // chain itself is serial, and on a vector of millions it would otherwise wait for memory at every step.
-            for (int64_t i = n - 1; i >= 1; i -= AHEAD) {
-                const int cnt = (int)std::min<int64_t>(AHEAD, i);
-                for (int k = 0; k < cnt; ++k) {
-                    const uint32_t top = (uint32_t)(i - k);
-                    const uint32_t mask = 0xFFFFFFFFu >> __builtin_clz(top);
-                    uint32_t j;
-                    while ((j = rng.next() & mask) > top) {}
-                    js[k] = j;
-                    __builtin_prefetch(&idx[j], 1);
+        uint64_t done = 0, blk = 0;
+        const uint64_t n_blocks = (total + BLK - 1) / BLK;
+        auto wait_block = [&](uint64_t b) { while (produced.load(std::memory_order_acquire) <= b) std::this_thread::yield(); };
+        for (int32_t r = 0; r < reps; ++r) {
+            uint64_t left = per_rep;
+            int64_t i = n - 1;
+            while (left > 0) {
+                wait_block(blk);
+                const uint32_t* js = &ring[(size_t)(blk % NBLK) * BLK];
+                const uint64_t in_blk = std::min<uint64_t>(BLK, total - blk * BLK);
+                const uint64_t at = done - blk * BLK;                       // position inside the block (a repeat may end mid-block)
+                const uint64_t cnt = std::min<uint64_t>(in_blk - at, left);
+                if (at == 0 && blk + 1 < n_blocks && produced.load(std::memory_order_acquire) > blk + 1) {
+                    const uint32_t* nx = &ring[(size_t)((blk + 1) % NBLK) * BLK];    // targets of the next block, if it is there already
+                    const uint64_t nn = std::min<uint64_t>(BLK, total - (blk + 1) * BLK);
+                    for (uint64_t k = 0; k < nn; ++k) __builtin_prefetch(&idx[nx[k]], 1);
                 }
-                for (int k = 0; k < cnt; ++k) std::swap(idx[(size_t)(i - k)], idx[js[k]]);
+                for (uint64_t k = 0; k < cnt; ++k, --i) std::swap(idx[(size_t)i], idx[js[at + k]]);
+                done += cnt;
+                left -= cnt;
+                if (at + cnt == in_blk) {
+                    ++blk;
+                    consumed.store(blk, std::memory_order_release);
+                }
             }
-            // the shuffled vector is applied to the already permuted column: effective source index e_r = e_{r-1}[idx].
-            // That gather runs on a second thread, from a snapshot, while the next shuffle proceeds.
             int32_t* cur = out + (size_t)r * (size_t)n;
             if (composer.joinable()) composer.join();
-            if (r == 0) std::memcpy(cur, idx.data(), (size_t)n * sizeof(int32_t));
-            else {
+            if (r == 0) {
+                std::memcpy(cur, idx.data(), (size_t)n * sizeof(int32_t));
+                ready.store(1, std::memory_order_release);
+            } else {
                 std::vector<int32_t>& sn = snap[r & 1];
                 sn = idx;
                 const int32_t* prev = cur - n;
                 const int32_t* src = sn.data();
-                composer = std::thread([cur, prev, src, n] { for (int64_t i = 0; i < n; ++i) cur[i] = prev[src[i]]; });
+                const int64_t nn = n;
+                std::atomic<int>* flag = &ready;
+                composer = std::thread([cur, prev, src, nn, flag, r] {
+                    for (int64_t k = 0; k < nn; ++k) cur[k] = prev[src[k]];
+                    flag->store(r + 1, std::memory_order_release);
+                });
             }
         }
         if (composer.joinable()) composer.join();
+        drawer.join();
+    }
+};
+}  // namespace
+
+int hfe_perm_indices(uint32_t seed, int64_t n, int32_t n_repeats, int32_t* out) {
+    if (n < 0 || n > 0x7FFFFFFF || n_repeats < 0 || (!out && n > 0 && n_repeats > 0))
+        return fail(HFE_ERR_INVALID_ARGUMENT, "bad permutation request");
+    ShuffleJob job;
+    job.seed = seed;
+    job.n = n;
+    job.reps = n_repeats;
+    job.out = out;
+    job.run();
+    if (job.failed.load()) return fail(HFE_ERR_INVALID_ARGUMENT, "permutation vectors: out of host memory");
+    return HFE_OK;
+}
+
+int hfe_permutation_passes(const hfe_model* model, const float* x, int64_t n, int64_t ld, const uint8_t* y, uint32_t seed,
+                           int32_t n_repeats, int32_t n_jobs, const int32_t* job_col, const int32_t* job_rep,
+                           int32_t* perm_host, int32_t* perm_dev, unsigned long long* scores, uint32_t* flags,
+                           uint32_t* status, void* stream) {
+    if (n_jobs < 0 || n_repeats < 0 || (n_jobs > 0 && (!job_col || !job_rep || !scores || !y)))
+        return fail(HFE_ERR_INVALID_ARGUMENT, "bad permutation job list");
+    if (n < 0 || n > 0x7FFFFFFF) return fail(HFE_ERR_INVALID_ARGUMENT, "bad row count");
+    int last = -1;
+    for (int32_t k = 0; k < n_jobs; ++k) {
+        if (job_col[k] >= F) return fail(HFE_ERR_INVALID_ARGUMENT, "bad permutation column");
+        if (job_col[k] < 0) continue;
+        if (job_rep[k] < 0 || job_rep[k] >= n_repeats || job_rep[k] < last)
+            return fail(HFE_ERR_INVALID_ARGUMENT, "permutation jobs must come in ascending repeat order");
+        last = job_rep[k];
+    }
+    if (last >= 0 && (!perm_host || !perm_dev)) return fail(HFE_ERR_INVALID_ARGUMENT, "null index-vector buffers");
+    try {
+        ShuffleJob job;
+        job.seed = seed;
+        job.n = n;
+        job.reps = last + 1;                       // vectors beyond the last one asked for are not made
+        job.out = perm_host;
+        std::thread maker([&job] { job.run(); });
+        struct Join { std::thread& t; ~Join() { if (t.joinable()) t.join(); } } join{maker};
+        cudaStream_t s = static_cast<cudaStream_t>(stream);
+        int uploaded = 0;
+        for (int32_t k = 0; k < n_jobs; ++k) {
+            const int col = job_col[k], r = job_rep[k];
+            if (col >= 0) {
+                while (job.ready.load(std::memory_order_acquire) <= r) std::this_thread::yield();
+                if (job.failed.load()) return fail(HFE_ERR_INVALID_ARGUMENT, "permutation vectors: out of host memory");
+                for (; uploaded <= r; ++uploaded)
+                    HFE_CUDA_TRY(cudaMemcpyAsync(perm_dev + (size_t)uploaded * (size_t)n, perm_host + (size_t)uploaded * (size_t)n,
+                                                 (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, s));
+            }
+            int rc = score_common(model, x, n, ld, col, col >= 0 ? perm_dev + (size_t)r * (size_t)n : nullptr, nullptr, nullptr,
+                                  nullptr, nullptr, nullptr, y, scores + k, status, stream, false);
+            if (rc) return rc;
+            if (flags)
+                HFE_CUDA_TRY(cudaMemcpyAsync(flags + k, status, sizeof(uint32_t), cudaMemcpyDeviceToDevice, s));
+        }
     } catch (const std::exception& e) {
-        return fail(HFE_ERR_INVALID_ARGUMENT, std::string("out of host memory: ") + e.what());
+        return fail(HFE_ERR_INVALID_ARGUMENT, std::string("permutation passes: ") + e.what());
     }
     return HFE_OK;
 }

@@ -83,30 +83,47 @@ def permutation_importance(clf, x, y, n_repeats: int = 5, random_state=None, ran
     y_dev = torch.from_numpy(y_idx).to(dev)
     rs = random_state if isinstance(random_state, np.random.RandomState) else np.random.RandomState(random_state)
     random_seed = rs.randint(np.iinfo(np.int32).max + 1)         # SK/inspection/_permutation_importance.py:278
-    if shuffle == "sklearn":
-        perms = torch.from_numpy(native_shuffled_indices(n, n_repeats, random_seed)).to(dev)
-    else:
-        perms = shuffled_indices_device(n, n_repeats, random_seed, dev)
     n_feat = clf.n_features_in_
     counts = torch.zeros(1 + n_feat * n_repeats, dtype=torch.int64, device=dev)
     status = clf.new_status()
     jobs = [(-1, 0)] + [(c, r) for c in range(n_feat) for r in range(n_repeats)]
     flags = torch.zeros(len(jobs), dtype=torch.int32, device=dev)      # status[0] of every pass (one array is reused)
-    # this rank's passes, column by column: one C call enqueues all repeats of a column back to back
     import ctypes as C
     lib, stream = capi.load_library(), torch.cuda.current_stream(dev).cuda_stream
     mine = list(range(len(jobs) * rank // world, len(jobs) * (rank + 1) // world))      # a contiguous block of passes per rank
-    with torch.cuda.device(dev):
-        at = 0
-        while at < len(mine):
-            col = jobs[mine[at]][0]
-            run = [k for k in mine[at:] if jobs[k][0] == col]
-            sel = (C.c_int32 * len(run))(*[jobs[k][1] for k in run])
-            capi.check(lib.hfe_score_permuted(clf._handle, x.data_ptr(), n, x.stride(0), col,
-                                              perms.data_ptr() if col >= 0 else None, perms.stride(0), len(run), sel,
-                                              y_dev.data_ptr(), counts[run[0]:].data_ptr(), flags[run[0]:].data_ptr(),
-                                              status.data_ptr(), stream))
-            at += len(run)
+    if shuffle == "sklearn":
+        # one C call: host threads make scikit-learn's index vectors while the passes that need the earlier ones already
+        # run on the device; this rank's passes in ascending repeat order, results scattered back to their slots
+        order = sorted(mine, key=lambda k: (jobs[k][0] >= 0, jobs[k][1], jobs[k][0]))
+        job_col = (C.c_int32 * len(order))(*[jobs[k][0] for k in order])
+        job_rep = (C.c_int32 * len(order))(*[jobs[k][1] for k in order])
+        perms_host = np.empty((n_repeats, n), dtype=np.int32)
+        perms = torch.empty((n_repeats, n), dtype=torch.int32, device=dev)
+        counts_run = torch.zeros(max(len(order), 1), dtype=torch.int64, device=dev)
+        flags_run = torch.zeros(max(len(order), 1), dtype=torch.int32, device=dev)
+        with torch.cuda.device(dev):
+            capi.check(lib.hfe_permutation_passes(clf._handle, x.data_ptr(), n, x.stride(0), y_dev.data_ptr(),
+                                                  int(random_seed) & 0xFFFFFFFF, n_repeats, len(order), job_col, job_rep,
+                                                  perms_host.ctypes.data_as(C.c_void_p), perms.data_ptr(),
+                                                  counts_run.data_ptr(), flags_run.data_ptr(), status.data_ptr(), stream))
+        if order:
+            at = torch.tensor(order, dtype=torch.long, device=dev)
+            counts[at] = counts_run[:len(order)]
+            flags[at] = flags_run[:len(order)]
+    else:
+        perms = shuffled_indices_device(n, n_repeats, random_seed, dev)
+        # this rank's passes, column by column: one C call enqueues all repeats of a column back to back
+        with torch.cuda.device(dev):
+            at = 0
+            while at < len(mine):
+                col = jobs[mine[at]][0]
+                run = [k for k in mine[at:] if jobs[k][0] == col]
+                sel = (C.c_int32 * len(run))(*[jobs[k][1] for k in run])
+                capi.check(lib.hfe_score_permuted(clf._handle, x.data_ptr(), n, x.stride(0), col,
+                                                  perms.data_ptr() if col >= 0 else None, perms.stride(0), len(run), sel,
+                                                  y_dev.data_ptr(), counts[run[0]:].data_ptr(), flags[run[0]:].data_ptr(),
+                                                  status.data_ptr(), stream))
+                at += len(run)
     flags_host = flags.cpu().numpy()
     if (flags_host & capi.ROW_NONFINITE).any():
         raise ValueError("Input X contains NaN or infinity.")          # what scikit-learn's scorer raises
