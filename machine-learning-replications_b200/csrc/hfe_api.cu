@@ -660,6 +660,18 @@ struct Mt19937 {
         mt[623] = twist(mt[623], mt[0], mt[396]);
         pos = 0;
     }
+    void next_block(uint32_t* out) {            // the next 624 outputs at once (pos must be at a block boundary)
+        refill();
+        for (int k = 0; k < 624; ++k) {
+            uint32_t v = mt[k];
+            v ^= v >> 11;
+            v ^= (v << 7) & 0x9D2C5680u;
+            v ^= (v << 15) & 0xEFC60000u;
+            v ^= v >> 18;
+            out[k] = v;
+        }
+        pos = 624;
+    }
     uint32_t next() {
         if (pos >= 624) refill();
         uint32_t v = mt[pos++];
@@ -705,19 +717,37 @@ private:
         std::atomic<uint64_t> produced{0}, consumed{0};
         const uint64_t per_rep = (uint64_t)(n - 1), total = per_rep * (uint64_t)reps;
         std::thread drawer([&] {
+            // random_interval(top): 32-bit draws masked to the bits of top, rejected while above it.  The generator's outputs
+            // are made 624 at a time, and the rejection is branch-free: a draw is written to the next slot and the slot only
+            // advances if it was accepted (the mask changes only when top passes a power of two, so runs share it).
             Mt19937 rng(seed);
+            uint32_t words[624];
+            int wpos = 624;
             uint64_t made = 0;
+            uint32_t top = (uint32_t)per_rep;                         // i runs n-1 .. 1 in every repeat
             while (made < total) {
                 const uint64_t b = produced.load(std::memory_order_relaxed);
                 while (b - consumed.load(std::memory_order_acquire) >= (uint64_t)NBLK) std::this_thread::yield();
                 uint32_t* dst = &ring[(size_t)(b % NBLK) * BLK];
-                const int cnt = (int)std::min<uint64_t>(BLK, total - made);
-                for (int k = 0; k < cnt; ++k) {
-                    const uint32_t top = (uint32_t)(per_rep - (made + k) % per_rep);        // i runs n-1 .. 1 in every repeat
+                const uint32_t cnt = (uint32_t)std::min<uint64_t>(BLK, total - made);
+                uint32_t filled = 0;
+                while (filled < cnt) {
                     const uint32_t mask = 0xFFFFFFFFu >> __builtin_clz(top);
-                    uint32_t jv;
-                    while ((jv = rng.next() & mask) > top) {}
-                    dst[k] = jv;
+                    const uint32_t floor_top = (mask >> 1) + 1u;       // smallest top with this mask
+                    uint32_t need = std::min<uint32_t>(cnt - filled, top - floor_top + 1u);
+                    while (need > 0) {
+                        if (wpos == 624) { rng.next_block(words); wpos = 0; }
+                        const uint32_t avail = std::min<uint32_t>((uint32_t)(624 - wpos), need * 2u + 8u);
+                        for (uint32_t k = 0; k < avail && need > 0; ++k) {
+                            const uint32_t jv = words[wpos++] & mask;
+                            dst[filled] = jv;
+                            const uint32_t ok = jv <= top ? 1u : 0u;
+                            filled += ok;
+                            top -= ok;
+                            need -= ok;
+                        }
+                    }
+                    if (top == 0) top = (uint32_t)per_rep;             // next repeat
                 }
                 made += cnt;
                 produced.store(b + 1, std::memory_order_release);
@@ -738,12 +768,15 @@ private:
                 const uint64_t in_blk = std::min<uint64_t>(BLK, total - blk * BLK);
                 const uint64_t at = done - blk * BLK;                       // position inside the block (a repeat may end mid-block)
                 const uint64_t cnt = std::min<uint64_t>(in_blk - at, left);
-                if (at == 0 && blk + 1 < n_blocks && produced.load(std::memory_order_acquire) > blk + 1) {
-                    const uint32_t* nx = &ring[(size_t)((blk + 1) % NBLK) * BLK];    // targets of the next block, if it is there already
-                    const uint64_t nn = std::min<uint64_t>(BLK, total - (blk + 1) * BLK);
-                    for (uint64_t k = 0; k < nn; ++k) __builtin_prefetch(&idx[nx[k]], 1);
+                // the swap chain is serial and its targets are random: each target is prefetched PD steps ahead (a burst for
+                // a whole block would overflow the core's handful of fill buffers)
+                constexpr uint64_t PD = 24;
+                if (at == 0)
+                    for (uint64_t k = 0; k < std::min<uint64_t>(PD, in_blk); ++k) __builtin_prefetch(&idx[js[k]], 1);
+                for (uint64_t k = 0; k < cnt; ++k, --i) {
+                    if (at + k + PD < in_blk) __builtin_prefetch(&idx[js[at + k + PD]], 1);
+                    std::swap(idx[(size_t)i], idx[js[at + k]]);
                 }
-                for (uint64_t k = 0; k < cnt; ++k, --i) std::swap(idx[(size_t)i], idx[js[at + k]]);
                 done += cnt;
                 left -= cnt;
                 if (at + cnt == in_blk) {
