@@ -1014,9 +1014,22 @@ int predict_host_pipelined(const hfe_model* model, const double* x_rowmajor, int
         ~Drain() { for (auto& s : hp.slot) { if (s.busy) cudaStreamSynchronize(s.stream); s.busy = false; } }
     } drain{hp};
 
+#ifdef HFE_DEV
+    struct Report {
+        HostPool* pool; double t0, busy0, wait = 0;
+        ~Report() { std::fprintf(stderr, "[hfe host pipeline] total %.2f ms, threads busy %.2f ms, waiting for the device %.2f ms\n",
+                                 (HostPool::now() - t0) * 1e3, (pool->busy_seconds - busy0) * 1e3, wait * 1e3); }
+    } report{hp.pool, HostPool::now(), hp.pool->busy_seconds};
+#endif
     auto retire = [&](HostSlot& s) -> int {
         if (!s.busy) return HFE_OK;
+#ifdef HFE_DEV
+        const double w0 = HostPool::now();
+#endif
         HFE_CUDA_TRY(cudaEventSynchronize(s.done));
+#ifdef HFE_DEV
+        report.wait += HostPool::now() - w0;
+#endif
         s.busy = false;
         const uint32_t* st = reinterpret_cast<const uint32_t*>(s.h_out + hp.h_off_status);
         flags |= st[0] | st[HFE_STATUS_HEADER_WORDS];

@@ -14,6 +14,7 @@
 #pragma once
 
 #include <atomic>
+#include <chrono>
 #include <condition_variable>
 #include <functional>
 #include <thread>
@@ -44,7 +45,14 @@ public:
         for (auto& w : workers_) w.join();
     }
     int size() const { return n_; }
+#ifdef HFE_DEV
+    double busy_seconds = 0;             // wall time spent inside run() (development builds)
+    static double now() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+#endif
     void run(const std::function<void(int, int)>& fn) {
+#ifdef HFE_DEV
+        struct Timer { double& acc; double t0; ~Timer() { acc += now() - t0; } } timer{busy_seconds, now()};
+#endif
         if (n_ == 1) { fn(0, 1); return; }
         fn_ = &fn;
         pending_.store(n_ - 1, std::memory_order_relaxed);
