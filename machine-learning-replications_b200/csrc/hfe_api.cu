@@ -1016,9 +1016,9 @@ int predict_host_pipelined(const hfe_model* model, const double* x_rowmajor, int
 
 #ifdef HFE_DEV
     struct Report {
-        HostPool* pool; double t0, busy0, wait = 0;
-        ~Report() { std::fprintf(stderr, "[hfe host pipeline] total %.2f ms, threads busy %.2f ms, waiting for the device %.2f ms\n",
-                                 (HostPool::now() - t0) * 1e3, (pool->busy_seconds - busy0) * 1e3, wait * 1e3); }
+        HostPool* pool; double t0, busy0, wait = 0, widen = 0;
+        ~Report() { std::fprintf(stderr, "[hfe host pipeline] total %.2f ms, threads busy %.2f ms (of which widening the results %.2f ms), waiting for the device %.2f ms\n",
+                                 (HostPool::now() - t0) * 1e3, (pool->busy_seconds - busy0) * 1e3, widen * 1e3, wait * 1e3); }
     } report{hp.pool, HostPool::now(), hp.pool->busy_seconds};
 #endif
     auto retire = [&](HostSlot& s) -> int {
@@ -1034,6 +1034,9 @@ int predict_host_pipelined(const hfe_model* model, const double* x_rowmajor, int
         const uint32_t* st = reinterpret_cast<const uint32_t*>(s.h_out + hp.h_off_status);
         flags |= st[0] | st[HFE_STATUS_HEADER_WORDS];
         const int64_t begin = s.begin, rows = s.rows;
+#ifdef HFE_DEV
+        struct Widen { double& acc; HostPool* pool; double b0; ~Widen() { acc += pool->busy_seconds - b0; } } widen_timer{report.widen, hp.pool, hp.pool->busy_seconds};
+#endif
         hp.pool->run([&](int t, int T) {
             const int64_t r0 = rows * t / T, r1 = rows * (t + 1) / T;
             if (r1 <= r0) return;
