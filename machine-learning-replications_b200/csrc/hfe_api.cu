@@ -757,7 +757,6 @@ private:
         for (int64_t i = 0; i < n; ++i) idx[(size_t)i] = (int32_t)i;
         std::thread composer;
         uint64_t done = 0, blk = 0;
-        const uint64_t n_blocks = (total + BLK - 1) / BLK;
         auto wait_block = [&](uint64_t b) { while (produced.load(std::memory_order_acquire) <= b) std::this_thread::yield(); };
         for (int32_t r = 0; r < reps; ++r) {
             uint64_t left = per_rep;
@@ -997,6 +996,13 @@ int hfe_predict_proba_noalloc(const hfe_model* model, const float* x, int64_t n,
 
 namespace {
 // Large host batches: see hfe_host.cuh.  `all_f64` reruns the batch on the float64 kernel (work-list overflow).
+//
+// One parallel region per chunk k, every thread of the pool in it:
+//   * thread 0 first hands chunk k-1 (narrowed in the previous region) to its slot's stream -- copy in, ingest, score, copies
+//     out, event -- so no thread waits while the CUDA calls are made;
+//   * everybody then takes work units off one counter: blocks of chunk k to narrow into slot k % 3, and blocks of the
+//     finished chunk k-3 (the slot's previous tenant, its event already waited for) to widen into the caller's arrays.
+// Units are small (32 K values / 16 K rows), so a thread that starts late or runs on a busy CPU just takes fewer.
 int predict_host_pipelined(const hfe_model* model, const double* x_rowmajor, int64_t n, double* proba_n2,
                            uint8_t* labels, double* decision, double* meta, bool all_f64) {
     const Model* m = model->impl;
@@ -1008,58 +1014,24 @@ int predict_host_pipelined(const hfe_model* model, const double* x_rowmajor, int
     HostPipeline& hp = *m->pipe;
     const int64_t C = hp.chunk;
     const int nm = m->n_members;
+    const int64_t n_chunks = (n + C - 1) / C;
     uint32_t flags = 0;
     struct Drain {                       // whatever happens, no stream still touches the slots when we leave
         HostPipeline& hp;
         ~Drain() { for (auto& s : hp.slot) { if (s.busy) cudaStreamSynchronize(s.stream); s.busy = false; } }
     } drain{hp};
-
 #ifdef HFE_DEV
     struct Report {
-        HostPool* pool; double t0, busy0, wait = 0, widen = 0;
-        ~Report() { std::fprintf(stderr, "[hfe host pipeline] total %.2f ms, threads busy %.2f ms (of which widening the results %.2f ms), waiting for the device %.2f ms\n",
-                                 (HostPool::now() - t0) * 1e3, (pool->busy_seconds - busy0) * 1e3, widen * 1e3, wait * 1e3); }
+        HostPool* pool; double t0, busy0, wait = 0;
+        ~Report() { std::fprintf(stderr, "[hfe host pipeline] total %.2f ms, threads busy %.2f ms, waiting for the device %.2f ms\n",
+                                 (HostPool::now() - t0) * 1e3, (pool->busy_seconds - busy0) * 1e3, wait * 1e3); }
     } report{hp.pool, HostPool::now(), hp.pool->busy_seconds};
 #endif
-    auto retire = [&](HostSlot& s) -> int {
-        if (!s.busy) return HFE_OK;
-#ifdef HFE_DEV
-        const double w0 = HostPool::now();
-#endif
-        HFE_CUDA_TRY(cudaEventSynchronize(s.done));
-#ifdef HFE_DEV
-        report.wait += HostPool::now() - w0;
-#endif
-        s.busy = false;
-        const uint32_t* st = reinterpret_cast<const uint32_t*>(s.h_out + hp.h_off_status);
-        flags |= st[0] | st[HFE_STATUS_HEADER_WORDS];
-        const int64_t begin = s.begin, rows = s.rows;
-#ifdef HFE_DEV
-        struct Widen { double& acc; HostPool* pool; double b0; ~Widen() { acc += pool->busy_seconds - b0; } } widen_timer{report.widen, hp.pool, hp.pool->busy_seconds};
-#endif
-        hp.pool->run([&](int t, int T) {
-            const int64_t r0 = rows * t / T, r1 = rows * (t + 1) / T;
-            if (r1 <= r0) return;
-            if (proba_n2)
-                widen_proba(reinterpret_cast<const float*>(s.h_out) + 2 * r0, proba_n2 + 2 * (begin + r0), (size_t)(r1 - r0));
-            if (labels) std::memcpy(labels + begin + r0, s.h_out + hp.h_off_lab + r0, (size_t)(r1 - r0));
-            if (decision)
-                std::memcpy(decision + begin + r0, s.h_out + hp.h_off_dec + r0 * sizeof(double), (size_t)(r1 - r0) * sizeof(double));
-            if (meta)
-                std::memcpy(meta + (begin + r0) * nm, s.h_out + hp.h_off_meta + r0 * nm * sizeof(double),
-                            (size_t)(r1 - r0) * nm * sizeof(double));
-        });
-        return HFE_OK;
-    };
 
-    int k = 0;
-    bool bytes_ok = true;
-    for (int64_t begin = 0; begin < n; begin += C, ++k) {
+    // thread 0, inside a region: chunk `k` (narrowed, in its slot) goes to the device
+    auto enqueue = [&](int64_t k) -> int {
         HostSlot& s = hp.slot[k % HOST_SLOTS];
-        int rc = retire(s);
-        if (rc) return rc;
-        const int64_t rows = std::min(C, n - begin);
-        const double* src = x_rowmajor + begin * F;
+        const int64_t rows = s.rows;
         float* d_raw = reinterpret_cast<float*>(s.d_buf + hp.off_raw);
         float* d_col = reinterpret_cast<float*>(s.d_buf + hp.off_col);
         float* d_out = reinterpret_cast<float*>(s.d_buf + hp.off_out);
@@ -1067,30 +1039,11 @@ int predict_host_pipelined(const hfe_model* model, const double* x_rowmajor, int
         double* d_dec = decision ? reinterpret_cast<double*>(s.d_buf + hp.off_dec) : nullptr;
         double* d_meta = meta ? reinterpret_cast<double*>(s.d_buf + hp.off_meta) : nullptr;
         uint32_t* d_status = reinterpret_cast<uint32_t*>(s.d_buf + hp.off_status);     // [ingest header | scoring status]
-        // Wire format, chosen per chunk: while every value so far in this call was an integer in [0, 255] (cohort variables
-        // are counts, classes and yes/no answers) the chunk crosses PCIe as bytes -- 17 instead of 68 per row, lossless, so
-        // the scores are the same bits; the first chunk that holds anything else is narrowed again to float32 and the rest
-        // of the call does not try bytes any more.
-        bool as_bytes = bytes_ok;
-        if (as_bytes) {
-            std::atomic<int> failed{0};
-            unsigned char* h_u8 = reinterpret_cast<unsigned char*>(s.h_in);
-            hp.pool->run([&](int t, int T) {
-                // thread shares start on 16-byte boundaries of the destination so that the streaming stores stay aligned
-                const int64_t total = rows * F;
-                const int64_t e0 = (total * t / T) & ~(int64_t)15, e1 = t + 1 == T ? total : (total * (t + 1) / T) & ~(int64_t)15;
-                if (e1 > e0 && !narrow_rows_u8(src + e0, h_u8 + e0, (size_t)(e1 - e0))) failed.store(1, std::memory_order_relaxed);
-            });
-            if (failed.load()) { as_bytes = false; bytes_ok = false; }
-        }
-        if (as_bytes) {
+        int rc;
+        if (s.as_bytes) {
             HFE_CUDA_TRY(cudaMemcpyAsync(d_raw, s.h_in, (size_t)rows * F, cudaMemcpyHostToDevice, s.stream));
             rc = hfe_ingest_rowmajor_u8(reinterpret_cast<const uint8_t*>(d_raw), rows, F, d_col, C, d_status, s.stream);
         } else {
-            hp.pool->run([&](int t, int T) {
-                const int64_t e0 = rows * F * t / T, e1 = rows * F * (t + 1) / T;
-                narrow_rows(src + e0, s.h_in + e0, (size_t)(e1 - e0));
-            });
             HFE_CUDA_TRY(cudaMemcpyAsync(d_raw, s.h_in, (size_t)rows * F * sizeof(float), cudaMemcpyHostToDevice, s.stream));
             rc = hfe_ingest_rowmajor_f32(d_raw, rows, F, d_col, C, d_status, s.stream);
         }
@@ -1107,13 +1060,91 @@ int predict_host_pipelined(const hfe_model* model, const double* x_rowmajor, int
         HFE_CUDA_TRY(cudaMemcpyAsync(s.h_out + hp.h_off_status, d_status, 2 * HFE_STATUS_HEADER_WORDS * sizeof(uint32_t),
                                      cudaMemcpyDeviceToHost, s.stream));
         HFE_CUDA_TRY(cudaEventRecord(s.done, s.stream));
-        s.begin = begin;
-        s.rows = rows;
         s.busy = true;
-    }
-    for (int i = 0; i < HOST_SLOTS; ++i) {               // oldest first
-        int rc = retire(hp.slot[(k + i) % HOST_SLOTS]);
-        if (rc) return rc;
+        return HFE_OK;
+    };
+
+    constexpr int64_t UNIT_VALUES = 1 << 15, UNIT_ROWS = 1 << 14;
+    // Wire format, chosen per chunk: while every value so far in this call was an integer in [0, 255] (cohort variables are
+    // counts, classes and yes/no answers) a chunk crosses PCIe as bytes -- 17 instead of 68 per row, lossless, so the scores
+    // are the same bits; the first chunk that holds anything else is narrowed again to float32 and the rest of the call does
+    // not try bytes any more.
+    bool bytes_ok = true;
+    for (int64_t k = 0; k < n_chunks + HOST_SLOTS; ++k) {
+        const bool has_narrow = k < n_chunks;                                     // chunk k -> slot k % 3
+        const bool has_enqueue = k >= 1 && k - 1 < n_chunks;                      // chunk k-1, narrowed last time round
+        const int64_t w = k - HOST_SLOTS;                                         // chunk to widen (shares the slot with chunk k)
+        const bool has_widen = w >= 0 && w < n_chunks;
+        HostSlot& s = hp.slot[k % HOST_SLOTS];
+        int64_t w_begin = 0, w_rows = 0;
+        if (has_widen) {                                                          // its results must have arrived
+#ifdef HFE_DEV
+            const double w0 = HostPool::now();
+#endif
+            HFE_CUDA_TRY(cudaEventSynchronize(s.done));
+#ifdef HFE_DEV
+            report.wait += HostPool::now() - w0;
+#endif
+            s.busy = false;
+            const uint32_t* st = reinterpret_cast<const uint32_t*>(s.h_out + hp.h_off_status);
+            flags |= st[0] | st[HFE_STATUS_HEADER_WORDS];
+            w_begin = s.begin;
+            w_rows = s.rows;
+        }
+        const int64_t begin = k * C, rows = has_narrow ? std::min(C, n - begin) : 0;
+        const double* src = x_rowmajor + begin * F;
+        const int64_t total = rows * F;
+        const int64_t narrow_units = (total + UNIT_VALUES - 1) / UNIT_VALUES, widen_units = (w_rows + UNIT_ROWS - 1) / UNIT_ROWS;
+        const bool try_bytes = bytes_ok;
+        std::atomic<int64_t> next{0};
+        std::atomic<int> not_bytes{0}, enqueue_rc{HFE_OK};
+        unsigned char* h_u8 = reinterpret_cast<unsigned char*>(s.h_in);
+        const unsigned char* w_out = s.h_out;        // (the slot's output block is only rewritten by chunk k, enqueued next round)
+        hp.pool->run([&](int t, int) {
+            if (t == 0 && has_enqueue) enqueue_rc.store(enqueue(k - 1));
+            for (;;) {
+                const int64_t u = next.fetch_add(1, std::memory_order_relaxed);
+                if (u < narrow_units) {
+                    const int64_t e0 = u * UNIT_VALUES, e1 = std::min(total, e0 + UNIT_VALUES);
+                    if (try_bytes) {
+                        if (!not_bytes.load(std::memory_order_relaxed) && !narrow_rows_u8(src + e0, h_u8 + e0, (size_t)(e1 - e0)))
+                            not_bytes.store(1, std::memory_order_relaxed);
+                    } else {
+                        narrow_rows(src + e0, s.h_in + e0, (size_t)(e1 - e0));
+                    }
+                } else if (u < narrow_units + widen_units) {
+                    const int64_t r0 = (u - narrow_units) * UNIT_ROWS, r1 = std::min(w_rows, r0 + UNIT_ROWS);
+                    if (proba_n2)
+                        widen_proba(reinterpret_cast<const float*>(w_out) + 2 * r0, proba_n2 + 2 * (w_begin + r0), (size_t)(r1 - r0));
+                    if (labels) std::memcpy(labels + w_begin + r0, w_out + hp.h_off_lab + r0, (size_t)(r1 - r0));
+                    if (decision)
+                        std::memcpy(decision + w_begin + r0, w_out + hp.h_off_dec + r0 * sizeof(double), (size_t)(r1 - r0) * sizeof(double));
+                    if (meta)
+                        std::memcpy(meta + (w_begin + r0) * nm, w_out + hp.h_off_meta + r0 * nm * sizeof(double),
+                                    (size_t)(r1 - r0) * nm * sizeof(double));
+                } else {
+                    break;
+                }
+            }
+        });
+        if (enqueue_rc.load()) return enqueue_rc.load();
+        if (has_narrow) {
+            if (try_bytes && not_bytes.load()) {                                  // something that is not a small integer: float32 from here on
+                bytes_ok = false;
+                std::atomic<int64_t> again{0};
+                hp.pool->run([&](int, int) {
+                    for (;;) {
+                        const int64_t u = again.fetch_add(1, std::memory_order_relaxed);
+                        if (u >= narrow_units) break;
+                        const int64_t e0 = u * UNIT_VALUES, e1 = std::min(total, e0 + UNIT_VALUES);
+                        narrow_rows(src + e0, s.h_in + e0, (size_t)(e1 - e0));
+                    }
+                });
+            }
+            s.as_bytes = bytes_ok;
+            s.begin = begin;
+            s.rows = rows;
+        }
     }
     if (flags & HFE_ROW_NONFINITE) return fail(HFE_ERR_NONFINITE_INPUT, "Input X contains NaN or infinity");
     if ((flags & HFE_WORKLIST_OVERFLOW) && !all_f64) return -1;      // caller reruns on the float64 kernel

@@ -118,6 +118,7 @@ struct HostSlot {
     unsigned char* d_buf = nullptr;           // device: raw rows | column-major | outputs | status
     int64_t begin = 0, rows = 0;              // the chunk this slot currently carries
     bool busy = false;
+    bool as_bytes = false;                    // the chunk sits in h_in as uint8 (else float32)
 };
 
 struct HostPipeline {
