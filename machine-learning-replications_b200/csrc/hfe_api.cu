@@ -672,15 +672,6 @@ struct Mt19937 {
         }
         pos = 624;
     }
-    uint32_t next() {
-        if (pos >= 624) refill();
-        uint32_t v = mt[pos++];
-        v ^= v >> 11;
-        v ^= (v << 7) & 0x9D2C5680u;
-        v ^= (v << 15) & 0xEFC60000u;
-        v ^= v >> 18;
-        return v;
-    }
 };
 }  // namespace
 

@@ -207,6 +207,7 @@ __attribute__((target("avx2"))) inline void narrow_rows_avx2(const double* __res
     size_t i = 0;
     while (i < count && (reinterpret_cast<uintptr_t>(dst + i) & 31)) { dst[i] = (float)src[i]; ++i; }
     for (; i + 8 <= count; i += 8) {
+        _mm_prefetch(reinterpret_cast<const char*>(src + i + 128), _MM_HINT_T0);
         const __m128 lo = _mm256_cvtpd_ps(_mm256_loadu_pd(src + i));
         const __m128 hi = _mm256_cvtpd_ps(_mm256_loadu_pd(src + i + 4));
         _mm256_stream_ps(dst + i, _mm256_insertf128_ps(_mm256_castps128_ps256(lo), hi, 1));
@@ -258,6 +259,8 @@ __attribute__((target("avx2"))) inline bool narrow_rows_u8_avx2(const double* __
     __m256d bad = _mm256_setzero_pd();
     __m128i high = _mm_setzero_si128();
     for (; i + 16 <= count; i += 16) {
+        _mm_prefetch(reinterpret_cast<const char*>(src + i + 128), _MM_HINT_T0);
+        _mm_prefetch(reinterpret_cast<const char*>(src + i + 136), _MM_HINT_T0);
         __m128i out = _mm_setzero_si128();
         __m128i part[4];
         for (int k = 0; k < 4; ++k) {
@@ -277,7 +280,58 @@ __attribute__((target("avx2"))) inline bool narrow_rows_u8_avx2(const double* __
 }
 #endif
 
+#if defined(__x86_64__)
+// AVX-512 versions (half the instructions per value; the conversion, not memory, bounds the narrowing per thread)
+__attribute__((target("avx512f,avx512bw,avx512vl,avx512dq"))) inline bool narrow_rows_u8_avx512(const double* __restrict__ src, unsigned char* __restrict__ dst, size_t count) {
+    size_t i = 0;
+    while (i < count && (reinterpret_cast<uintptr_t>(dst + i) & 15)) {
+        if (!narrow_rows_u8_plain(src + i, dst + i, 1)) return false;
+        ++i;
+    }
+    __mmask8 bad = 0;
+    __m512i high = _mm512_setzero_si512();
+    for (; i + 16 <= count; i += 16) {
+        _mm_prefetch(reinterpret_cast<const char*>(src + i + 128), _MM_HINT_T0);           // 1 KB ahead of the loads
+        _mm_prefetch(reinterpret_cast<const char*>(src + i + 136), _MM_HINT_T0);
+        const __m512d v0 = _mm512_loadu_pd(src + i), v1 = _mm512_loadu_pd(src + i + 8);
+        const __m256i q0 = _mm512_cvttpd_epi32(v0), q1 = _mm512_cvttpd_epi32(v1);          // NaN / out of range -> 0x80000000
+        bad = (__mmask8)(bad | _mm512_cmp_pd_mask(_mm512_cvtepi32_pd(q0), v0, _CMP_NEQ_UQ) |
+                         _mm512_cmp_pd_mask(_mm512_cvtepi32_pd(q1), v1, _CMP_NEQ_UQ));
+        const __m512i q = _mm512_inserti64x4(_mm512_castsi256_si512(q0), q1, 1);
+        high = _mm512_or_si512(high, q);                                                    // any bit above the low byte (or the sign) set?
+        _mm_stream_si128(reinterpret_cast<__m128i*>(dst + i), _mm512_cvtepi32_epi8(q));     // the sixteen low bytes
+    }
+    _mm_sfence();
+    if (bad != 0) return false;
+    if (_mm512_test_epi32_mask(high, _mm512_set1_epi32(~0xFF)) != 0) return false;
+    return narrow_rows_u8_plain(src + i, dst + i, count - i);
+}
+
+__attribute__((target("avx512f,avx512bw,avx512vl,avx512dq"))) inline void narrow_rows_avx512(const double* __restrict__ src, float* __restrict__ dst, size_t count) {
+    size_t i = 0;
+    while (i < count && (reinterpret_cast<uintptr_t>(dst + i) & 63)) { dst[i] = (float)src[i]; ++i; }
+    for (; i + 16 <= count; i += 16) {
+        _mm_prefetch(reinterpret_cast<const char*>(src + i + 128), _MM_HINT_T0);
+        _mm_prefetch(reinterpret_cast<const char*>(src + i + 136), _MM_HINT_T0);
+        const __m256 lo = _mm512_cvtpd_ps(_mm512_loadu_pd(src + i));
+        const __m256 hi = _mm512_cvtpd_ps(_mm512_loadu_pd(src + i + 8));
+        _mm512_stream_ps(dst + i, _mm512_insertf32x8(_mm512_castps256_ps512(lo), hi, 1));
+    }
+    for (; i < count; ++i) dst[i] = (float)src[i];
+    _mm_sfence();
+}
+
+inline bool host_has_avx512() {
+    static const bool yes = __builtin_cpu_supports("avx512f") && __builtin_cpu_supports("avx512bw") &&
+                            __builtin_cpu_supports("avx512vl") && __builtin_cpu_supports("avx512dq");
+    return yes;
+}
+#endif
+
 inline bool narrow_rows_u8(const double* src, unsigned char* dst, size_t count) {
+#if defined(__x86_64__)
+    if (host_has_avx512()) return narrow_rows_u8_avx512(src, dst, count);
+#endif
 #if defined(__x86_64__)
     if (host_has_avx2()) return narrow_rows_u8_avx2(src, dst, count);
 #endif
@@ -286,6 +340,7 @@ inline bool narrow_rows_u8(const double* src, unsigned char* dst, size_t count) 
 
 inline void narrow_rows(const double* src, float* dst, size_t count) {
 #if defined(__x86_64__)
+    if (host_has_avx512()) { narrow_rows_avx512(src, dst, count); return; }
     if (host_has_avx2()) { narrow_rows_avx2(src, dst, count); return; }
 #endif
     narrow_rows_plain(src, dst, count);

@@ -51,7 +51,9 @@ int main(int argc, char** argv) {
                     const __m128i pick = _mm_setr_epi8(0, 4, 8, 12, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1);
                     __m256d bad = _mm256_setzero_pd();
                     __m128i high = _mm_setzero_si128();
+                    const size_t pd = argc > 2 ? (size_t)atoi(argv[2]) : 0;
                     for (size_t i = a; i + 16 <= b; i += 16) {
+                        if (pd) { _mm_prefetch(reinterpret_cast<const char*>(x + i + pd), _MM_HINT_T0); _mm_prefetch(reinterpret_cast<const char*>(x + i + pd + 8), _MM_HINT_T0); }
                         __m128i part[4];
                         for (int k = 0; k < 4; ++k) {
                             const __m256d v = _mm256_loadu_pd(x + i + 4 * k);
