@@ -308,9 +308,12 @@ def e2e_legs(ctx, clf, x, out, n, args):
     for _ in range(2):
         proba = clf.predict_proba(X64)
     ctx.barrier()
+    calls = []
     t0 = time.perf_counter()
     for _ in range(steps):
+        c0 = time.perf_counter()
         proba = clf.predict_proba(X64)
+        calls.append(time.perf_counter() - c0)
     dt = ctx.reduce((time.perf_counter() - t0) / steps, "max")
     diff = float(np.abs(proba[:, 1] - out[:rows, 1].cpu().numpy().astype(np.float64)).max())
     # the library sends a chunk as bytes when all its values are integers in [0, 255] (lossless), else as float32
@@ -323,7 +326,7 @@ def e2e_legs(ctx, clf, x, out, n, args):
                          "float64 [rows,2]; hfe_predict_host narrows on host threads into pinned chunks (bytes when the "
                          "chunk is an integer cohort, else float32: what crosses PCIe), 3 chunks in flight over 3 streams, "
                          "ingest + scoring + D2H per chunk",
-                  "max_abs_diff_vs_device_path": diff}
+                  "max_abs_diff_vs_device_path": diff, "ms_per_call_rank0": [round(c * 1e3, 2) for c in calls]}
     del X64, proba
     # (2) the same device path fed from pinned float32 / uint8 tensors (no host-side narrowing)
     x_host = torch.empty((rows, 17), dtype=torch.float32).pin_memory()
