@@ -95,7 +95,9 @@ typedef struct hfe_model_info {
 
 /* Replaces pickle.load('./hf_predict_model.pkl') (predict_hf.py:33-34): validates the flat blob written by
  * export/blob.py (header, CRC-32, section shapes, tree topology, the n_support consistency check of
- * SK/svm/_base.py:680-686), derives the device tables and uploads them to `device`.  Allocates; call once. */
+ * SK/svm/_base.py:680-686), derives the device tables and uploads them to `device`, then checks the float32 guard bands
+ * against this model (hfe_model_calibrate_guards(model, 1): 65 536 probe rows, ~10 ms).  Allocates and synchronises; call
+ * once. */
 int hfe_model_create(const void* blob, size_t blob_bytes, int device, hfe_model** out_model);
 void hfe_model_destroy(hfe_model* model);
 int hfe_model_get_info(const hfe_model* model, hfe_model_info* out_info);
@@ -241,8 +243,12 @@ int hfe_binary_metrics(const float* proba_n2, const uint8_t* y, int64_t n, float
                        unsigned long long* confusion, uint32_t* hist, void* stream);
 
 /* Host-buffer convenience used by the facade for numpy inputs: copies X (row-major float64, host) to the device,
- * ingests, scores, copies P back (float64 [n,2]; p0 = 1 - p1) and synchronises.  Large batches use stream-ordered
- * temporaries.  Up to 4096 rows (predict_hf.py:36 scores one patient) skip the copies altogether: the rows are placed
+ * ingests, scores, copies P back (float64 [n,2]; p0 = 1 - p1) and synchronises.  From 65 536 rows on (train_ensemble_public.py:62
+ * on a big cohort) the batch goes through a chunk pipeline the handle owns and builds on first use -- three pinned /
+ * device slots of 262 144 rows with a stream each and a pool of host threads (one per CPU the process may run on, at most
+ * 16; environment HFE_HOST_THREADS): the threads narrow the caller's float64 rows into a pinned chunk (float32, or bytes
+ * while every value is an integer in [0, 255] -- lossless), the slot's stream copies, ingests, scores and copies back, the
+ * threads widen the probabilities into the caller's array; one such call at a time per handle.  Up to 4096 rows (predict_hf.py:36 scores one patient) skip the copies altogether: the rows are placed
  * in pinned memory mapped into the device address space (a block owned by the handle, one caller at a time) and one
  * kernel -- a warp per row, on the float64 path -- evaluates them and writes the results back.
  * labels / decision / meta may be NULL.  Returns HFE_ERR_NONFINITE_INPUT when X holds NaN/Inf. */
