@@ -66,13 +66,20 @@ class _ResultPool:
         self._lock = threading.Lock()
 
     def _give_back(self, owner):
+        import sys
         with self._lock:
+            if len(self._free) >= self.MAX_HELD:
+                # full: let go of the oldest buffer a caller still holds on to (it stays theirs; it just will not be
+                # recycled), so results that live long do not clog the pool
+                for k in range(len(self._free)):
+                    if sys.getrefcount(self._free[k][1]) > 2:
+                        self._free.pop(k)
+                        break
             held = sum(b for b, _ in self._free)
             if len(self._free) < self.MAX_HELD and held + owner.nbytes <= self.MAX_HELD_BYTES:
                 self._free.append((owner.nbytes, owner))
 
     def empty(self, shape, dtype):
-        import weakref
         dtype = np.dtype(dtype)
         nbytes = int(np.prod(shape)) * dtype.itemsize
         if nbytes < self.MIN_BYTES:
@@ -88,9 +95,11 @@ class _ResultPool:
                     break
         if owner is None:
             owner = np.empty(nbytes, dtype=np.uint8)
-        root = owner.view(dtype)                                # every view the caller takes has this array as its base
-        weakref.finalize(root, self._give_back, owner)
-        return root.reshape(shape)
+        # numpy collapses base chains: the array handed out and every view of it keep `owner` alive, so its reference count
+        # tells whether the caller still uses the buffer; it is listed for reuse right away and taken when that count drops
+        out = owner.view(dtype).reshape(shape)
+        self._give_back(owner)
+        return out
 
 
 _results = _ResultPool()

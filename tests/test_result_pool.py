@@ -37,3 +37,16 @@ def test_result_buffers_are_recycled_only_when_nothing_refers_to_them(pkg):
     assert small.shape == (10, 2)
     other = pool.empty((1_000_000,), np.uint8)
     assert other.dtype == np.uint8 and other.shape == (1_000_000,)
+
+
+def test_long_lived_results_do_not_clog_the_pool(pkg):
+    pool = pkg.facade._ResultPool()
+    shape = (600_000, 2)
+    keep = [pool.empty(shape, np.float64) for _ in range(5)]            # the caller holds on to five results
+    assert len({_addr(a) for a in keep}) == 5
+    x = pool.empty(shape, np.float64)
+    addr = _addr(x)
+    del x
+    gc.collect()
+    y = pool.empty(shape, np.float64)                                   # the released one is recycled all the same
+    assert _addr(y) == addr and len(pool._free) <= pool.MAX_HELD
