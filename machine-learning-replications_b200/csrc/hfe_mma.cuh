@@ -56,10 +56,13 @@ constexpr int MMA_THREADS = 32 * (MMA_ISSUE_WARP + 4);          // 640: the issu
 // Registers per thread and warpgroup (setmaxnreg; the kernel starts every thread at 96 = what 640 threads leave of 64 K):
 // the float64 finishing code wants the most, the issuing warpgroup next to none.  What one group gives up another can take:
 // the sum over the five groups must not exceed 5 x 96 (the pool is what the CTA was launched with; asking for more blocks forever).
-#ifndef HFE_MMA_REGS
-#define HFE_MMA_REGS 80, 144, 104, 48
+#ifndef HFE_MMA_REG_P
+#define HFE_MMA_REG_P 80
+#define HFE_MMA_REG_F 144
+#define HFE_MMA_REG_E 104
+#define HFE_MMA_REG_I 48
 #endif
-constexpr int MMA_REGS[4] = {HFE_MMA_REGS};               // producers, finishers, exponent warps (each of two groups), issue group
+constexpr int MMA_REGS[4] = {HFE_MMA_REG_P, HFE_MMA_REG_F, HFE_MMA_REG_E, HFE_MMA_REG_I};               // producers, finishers, exponent warps (each of two groups), issue group
 static_assert(MMA_REGS[0] + MMA_REGS[1] + 2 * MMA_REGS[2] + MMA_REGS[3] <= 5 * 96, "register pool of the CTA");
 constexpr int MMA_A_STAGES = 5;                          // two tiles in the tensor core / exponent warps, three produced ahead
 constexpr int MMA_A_CHUNKS = 12;                         // 16-byte K chunks per row: H0 H1 H2 0 | M0 M1 M2 0 | L0 L1 L2 0
