@@ -9,6 +9,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("HFE_LIB") or os.path.join(_HERE, "libhfe.so")   # HFE_LIB: development override
 
 HFE_OK = 0
+HFE_ERR_INVALID_ARGUMENT = 1
 HFE_ERR_NONFINITE_INPUT = 5
 HFE_ERR_TOO_LARGE = 6
 STATUS_HEADER_WORDS = 4

@@ -48,3 +48,22 @@ def test_native_shuffles_are_numpys(pkg, cuda_lib):
     insp = pkg.inspection
     for n, reps, seed in ((0, 2, 1), (1, 3, 5), (2, 2, 7), (3, 4, 0), (255, 3, 9), (256, 3, 9), (257, 5, 4294967295), (513, 2, 77), (50_000, 5, 2020), (65_537, 2, 123456789)):
         assert np.array_equal(insp.native_shuffled_indices(n, reps, seed), insp.shuffled_indices(n, reps, seed)), (n, seed)
+
+
+def test_permutation_passes_refuses_bad_job_lists(pkg, cuda_lib):
+    """hfe_permutation_passes validates its job list before it touches a device: repeats must ascend and stay in range."""
+    import ctypes as C
+    lib = cuda_lib
+    cols = (C.c_int32 * 3)(0, 1, 2)
+    host = np.zeros((2, 8), dtype=np.int32)
+    dummy = C.c_void_p(16)                                    # never dereferenced: validation comes first
+
+    def call(reps, n_repeats=2, n_jobs=3):
+        r = (C.c_int32 * 3)(*reps)
+        return lib.hfe_permutation_passes(None, dummy, 8, 8, dummy, 1, n_repeats, n_jobs, cols, r,
+                                          host.ctypes.data_as(C.c_void_p), dummy, dummy, None, dummy, None)
+
+    assert call((1, 0, 1)) == pkg.capi.HFE_ERR_INVALID_ARGUMENT          # descending repeat
+    assert call((0, 1, 2)) == pkg.capi.HFE_ERR_INVALID_ARGUMENT          # repeat out of range
+    assert call((0, 0, 1), n_jobs=-1) == pkg.capi.HFE_ERR_INVALID_ARGUMENT
+    assert b"ascending" in lib.hfe_last_error_string() or b"job list" in lib.hfe_last_error_string()
