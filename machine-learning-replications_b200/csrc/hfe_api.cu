@@ -1055,7 +1055,10 @@ int predict_host_pipelined(const hfe_model* model, const double* x_rowmajor, int
         return HFE_OK;
     };
 
-    constexpr int64_t UNIT_VALUES = 1 << 15, UNIT_ROWS = 1 << 14;
+#ifndef HFE_UNIT_VALUES
+#define HFE_UNIT_VALUES (1 << 15)
+#endif
+    constexpr int64_t UNIT_VALUES = HFE_UNIT_VALUES, UNIT_ROWS = 1 << 14;
     // Wire format, chosen per chunk: while every value so far in this call was an integer in [0, 255] (cohort variables are
     // counts, classes and yes/no answers) a chunk crosses PCIe as bytes -- 17 instead of 68 per row, lossless, so the scores
     // are the same bits; the first chunk that holds anything else is narrowed again to float32 and the rest of the call does
